@@ -1,0 +1,179 @@
+/*
+ * wheatsplat.h -- C ABI of libwheatsplat.so, the B200 (sm_100a) Gaussian-splatting hot path.
+ *
+ * This is the drop-in boundary for the three CUDA submodules Wheat3DGS calls
+ * (paths below are into the reference tree, /root/reference/submodules/):
+ *
+ *   DGR = diff-gaussian-rasterization   pybind _C.rasterize_gaussians / _backward / mark_visible
+ *                                       (DGR/ext.cpp:15-19, DGR/rasterize_points.h:18-70)
+ *   FSR = flashsplat-rasterization      same names, + gt_mask / unique_label / num_obj
+ *                                       (FSR/rasterize_points.h:18-46)
+ *   KNN = simple-knn                    _C.distCUDA2 (KNN/ext.cpp:15-17, KNN/spatial.cu:15-26)
+ *
+ * Conventions
+ *   - plain C: raw device pointers, ints, floats; no C++ types, no exceptions cross the ABI.
+ *   - NULL pointer = "not provided" (the reference passes empty tensors whose data_ptr is
+ *     nullptr, DGR/diff_gaussian_rasterization/__init__.py:200-210; tested at
+ *     DGR/cuda_rasterizer/forward.cu:205,241).
+ *   - the CALLER owns all memory (outputs and scratch).  The library never allocates device
+ *     memory on the hot path.  Scratch sizes come from ws_*_bytes().  The reference instead
+ *     grows three torch byte tensors through std::function callbacks
+ *     (DGR/rasterize_points.cu:27-33,78-80); the forward is therefore split in two calls at
+ *     exactly the point where the reference does its D2H read of num_rendered
+ *     (DGR/cuda_rasterizer/rasterizer_impl.cu:282): ws_forward_prepare returns num_rendered,
+ *     the caller sizes the binning scratch, ws_forward_render finishes.
+ *   - every call takes the CUDA stream to run on (the reference uses the legacy default
+ *     stream everywhere); calls are re-entrant per (device, stream) as long as scratch
+ *     buffers are not shared.
+ *   - return value: >= 0 success, < 0 error (WS_E_*); ws_last_error() gives the text.
+ *   - matrices are the reference's: viewmatrix/projmatrix are float[16] stored transposed
+ *     (row-vector convention), indexed m[0],m[4],m[8],m[12] for the first output component
+ *     (DGR/cuda_rasterizer/auxiliary.h:58-66).
+ */
+#ifndef WHEATSPLAT_H_INCLUDED
+#define WHEATSPLAT_H_INCLUDED
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct CUstream_st *ws_stream_t;
+
+#define WS_OK 0
+#define WS_E_INVALID (-1)   /* bad argument (shape, NULL where required, both/neither of an either-or pair) */
+#define WS_E_SCRATCH (-2)   /* scratch buffer too small */
+#define WS_E_CUDA (-3)      /* a CUDA runtime call or kernel launch failed */
+#define WS_E_UNSUPPORTED (-4)
+
+#define WS_ABI_VERSION 1
+
+/* Per-view constants = GaussianRasterizationSettings
+ * (DGR/diff_gaussian_rasterization/__init__.py:160-172; FSR adds mask_grad, num_obj:
+ * FSR/flashsplat_rasterization/__init__.py:201-215 -- num_obj travels in ws_flash). */
+typedef struct ws_view {
+    int32_t image_height;
+    int32_t image_width;
+    float tanfovx;
+    float tanfovy;
+    float scale_modifier;
+    int32_t sh_degree;        /* active degree D, 0..3 */
+    int32_t prefiltered;      /* callers always pass 0 (gaussian_renderer/__init__.py:51,143) */
+    int32_t debug;            /* !=0: synchronise and check after every stage (auxiliary.h:166-173) */
+    const float *bg;          /* device float[3] */
+    const float *viewmatrix;  /* device float[16] */
+    const float *projmatrix;  /* device float[16] */
+    const float *campos;      /* device float[3] */
+} ws_view;
+
+/* The Gaussians = the tensor arguments of rasterize_gaussians (DGR/rasterize_points.h:18-38). */
+typedef struct ws_gaussians {
+    int32_t P;                   /* number of Gaussians, means3D is [P,3] */
+    int32_t M;                   /* SH coefficients per Gaussian (sh is [P,M,3]); 0 if no SH */
+    const float *means3D;        /* [P,3] */
+    const float *shs;            /* [P,M,3] coefficient-major, RGB innermost, or NULL */
+    const float *colors_precomp; /* [P,3] or NULL; exactly one of shs / colors_precomp */
+    const float *opacities;      /* [P,1] post-sigmoid */
+    const float *scales;         /* [P,3] post-exp, or NULL */
+    const float *rotations;      /* [P,4] (w,x,y,z), NOT normalised in-kernel (forward.cu:127), or NULL */
+    const float *cov3D_precomp;  /* [P,6] or NULL; exactly one of (scales,rotations) / cov3D_precomp */
+} ws_gaussians;
+
+/* flashsplat additions (FSR/rasterize_points.cu:36-131).  Pass NULL for the plain DGR op. */
+typedef struct ws_flash {
+    int32_t num_obj;            /* used_count has num_obj+1 rows */
+    const float *gt_mask;       /* [H,W] float object id per pixel (truncated to int); required */
+    const int32_t *unique_label;/* [P] or NULL (FSR forward.cu:357-362) */
+    int32_t *out_contrib_num;   /* [1,H,W], written for every pixel */
+    float *used_count;          /* [num_obj+1,P]; ACCUMULATED into (+=): zero it for reference
+                                   semantics, or keep one buffer across views to sum votes */
+    float *image_xys;           /* [2,P]; caller pre-fills -1.0 (FSR/rasterize_points.cu:77) */
+    float *gs_depth;            /* [P];   caller pre-fills -0.1 (FSR/rasterize_points.cu:78) */
+} ws_flash;
+
+/* Gradients = the 8 tensors rasterize_gaussians_backward returns
+ * (DGR/rasterize_points.cu:207).  Every element of every non-NULL tensor is written
+ * (zeros included), so the caller may allocate them uninitialised -- the reference's
+ * torch::zeros fills (rasterize_points.cu:153-162) are not needed. */
+typedef struct ws_grads {
+    float *dL_dmeans2D;   /* [P,3]  (z = 0) */
+    float *dL_dcolors;    /* [P,3]  grad of colors_precomp / of the SH-evaluated RGB */
+    float *dL_dopacity;   /* [P,1] */
+    float *dL_dmeans3D;   /* [P,3] */
+    float *dL_dcov3D;     /* [P,6] */
+    float *dL_dsh;        /* [P,M,3] or NULL when M == 0 */
+    float *dL_dscales;    /* [P,3] */
+    float *dL_drotations; /* [P,4] */
+} ws_grads;
+
+int ws_abi_version(void);
+const char *ws_last_error(void);
+
+/* Scratch sizes in bytes.  geom depends on P, image on W*H, binning on num_rendered. */
+size_t ws_geom_bytes(int32_t P);
+size_t ws_image_bytes(int32_t width, int32_t height);
+size_t ws_binning_bytes(int64_t num_rendered, int32_t width, int32_t height);
+
+/* Forward, phase A: preprocessCUDA + prefix sum of tiles_touched
+ * (rasterizer_impl.cu:248-282).  Writes radii[P] (int32, every element) and, if fl != NULL,
+ * image_xys / gs_depth.  Synchronises `stream` once to read num_rendered (as the reference's
+ * cudaMemcpy at :282 does).  Returns num_rendered >= 0. */
+int64_t ws_forward_prepare(const ws_view *view, const ws_gaussians *g, int32_t *radii, void *geom,
+                           size_t geom_bytes, const ws_flash *fl, ws_stream_t stream);
+
+/* Forward, phase B: duplicateWithKeys, radix sort, identifyTileRanges, render
+ * (rasterizer_impl.cu:284-339).  out_color [3,H,W], out_depth [1,H,W], out_alpha [1,H,W];
+ * every pixel is written. */
+int ws_forward_render(const ws_view *view, const ws_gaussians *g, const int32_t *radii, void *geom,
+                      void *binning, size_t binning_bytes, void *image, size_t image_bytes,
+                      int64_t num_rendered, float *out_color, float *out_depth, float *out_alpha,
+                      const ws_flash *fl, ws_stream_t stream);
+
+/* Backward (rasterizer_impl.cu:343-446).  geom/binning/image are the buffers of the matching
+ * forward; out_alpha is the forward's alpha output (T_final = 1 - alpha, backward.cu:463). */
+int ws_backward(const ws_view *view, const ws_gaussians *g, const int32_t *radii, void *geom,
+                void *binning, void *image, int64_t num_rendered, const float *out_alpha,
+                const float *dL_dcolor, const float *dL_ddepth, const float *dL_dalpha,
+                const ws_grads *grads, const ws_flash *fl, ws_stream_t stream);
+
+/* markVisible (DGR/rasterize_points.cu:210-229): present[i] = (view-space z > 0.2). */
+int ws_mark_visible(int32_t P, const float *means3D, const float *viewmatrix, const float *projmatrix,
+                    uint8_t *present, ws_stream_t stream);
+
+/* simple-knn distCUDA2 (KNN/simple_knn.cu:186-222): mean squared distance to the 3 nearest
+ * neighbours.  Synchronises `stream` once (the reference syncs twice for its bbox). */
+size_t ws_knn_bytes(int32_t P);
+int ws_knn_dist2(int32_t P, const float *points, float *mean_dists, void *scratch, size_t scratch_bytes,
+                 ws_stream_t stream);
+
+/* multi_instance_opt (run_3d_seg.py:54-72): labels[i,j] = argmax over normalize([sum_j - A_ij, A_ij])
+ * with gamma added to row 0.  all_contrib float[num_rows,P] -> labels uint8[num_rows,P]. */
+int ws_multi_instance_opt(int32_t num_rows, int32_t P, const float *all_contrib, float gamma,
+                          uint8_t *labels, ws_stream_t stream);
+
+/* The stable LSD radix sort the rasterizer uses (replaces cub::DeviceRadixSort::SortPairs,
+ * rasterizer_impl.cu:304-309), exposed for parity tests: sorts (u64 key, u32 value) pairs on
+ * key bits [0, end_bit).  Results land in keys_out / vals_out; *_in are clobbered. */
+size_t ws_sort_bytes(int64_t n);
+int ws_sort_pairs_u64(int64_t n, uint64_t *keys_in, uint64_t *keys_out, uint32_t *vals_in,
+                      uint32_t *vals_out, int32_t end_bit, void *scratch, size_t scratch_bytes,
+                      ws_stream_t stream);
+
+/* Parity/debug access to the internal arrays of a finished forward (device -> device copy
+ * into caller memory).  name is one of: "depths" f32[P], "means2D" f32[P,2],
+ * "conic_opacity" f32[P,4], "rgb" f32[P,3], "cov3D" f32[P,6], "tiles_touched" u32[P],
+ * "point_list_keys" u64[R], "point_list" u32[R], "ranges" u32[T,2], "n_contrib" u32[H,W].
+ * Returns bytes written or < 0. */
+int64_t ws_debug_fetch(const char *name, int32_t P, int32_t width, int32_t height, int64_t num_rendered,
+                       void *geom, void *binning, void *image, void *dst, size_t dst_bytes,
+                       ws_stream_t stream);
+
+/* Number of kernels this library launched since load (bench.py's gpu_launches counter). */
+int64_t ws_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* WHEATSPLAT_H_INCLUDED */

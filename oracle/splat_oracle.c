@@ -235,7 +235,7 @@ void so_preprocess(const so_scene *s, int *radii, float *means2D, float *depths,
         tiles_touched[idx] = 0;
         float x = s->means3D[3 * idx], y = s->means3D[3 * idx + 1], z = s->means3D[3 * idx + 2];
         float pvz = dot3_nv(x, v[2], y, v[6], z, v[10]) + v[14];
-        if (!(pvz > 0.2f)) continue; /* auxiliary.h:154 */
+        if (pvz <= 0.2f) continue; /* auxiliary.h:154 (NaN is NOT culled, as in the reference) */
         float hx = dot3_nv(x, pm[0], y, pm[4], z, pm[8]) + pm[12];
         float hy = dot3_nv(x, pm[1], y, pm[5], z, pm[9]) + pm[13];
         float hw = dot3_nv(x, pm[3], y, pm[7], z, pm[11]) + pm[15];
@@ -289,7 +289,7 @@ void so_mark_visible(int P, const float *means3D, const float *v, uint8_t *prese
     for (int idx = 0; idx < P; idx++) {
         float x = means3D[3 * idx], y = means3D[3 * idx + 1], z = means3D[3 * idx + 2];
         float pvz = dot3_nv(x, v[2], y, v[6], z, v[10]) + v[14];
-        present[idx] = pvz > 0.2f;
+        present[idx] = !(pvz <= 0.2f);
     }
 }
 

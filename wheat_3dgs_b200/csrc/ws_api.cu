@@ -1,0 +1,252 @@
+// ws_api.cu -- the C-ABI entry points declared in include/wheatsplat.h: argument checks,
+// scratch carving and stage sequencing.  No device memory is allocated here.
+#include <stdarg.h>
+#include <string.h>
+#include "ws_common.cuh"
+
+namespace ws {
+
+static thread_local char g_err[512] = "";
+long long g_launch_count = 0;
+
+void set_error(const char *fmt, ...)
+{
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+// DGR rasterizer_impl.cu:35-50
+static uint32_t get_higher_msb(uint32_t n)
+{
+    uint32_t msb = sizeof(n) * 4, step = msb;
+    while (step > 1) {
+        step /= 2;
+        if (n >> msb) msb += step; else msb -= step;
+    }
+    if (n >> msb) msb++;
+    return msb;
+}
+
+static int check_view_gauss(const char *who, const ws_view *v, const ws_gaussians *g, bool need_opacity = true)
+{
+    if (!v || !g) { set_error("%s: NULL view/gaussians", who); return WS_E_INVALID; }
+    if (g->P <= 0) { set_error("%s: P must be > 0 (the wrapper handles empty inputs)", who); return WS_E_INVALID; }
+    if (v->image_width <= 0 || v->image_height <= 0) { set_error("%s: bad image size", who); return WS_E_INVALID; }
+    if (!v->bg || !v->viewmatrix || !v->projmatrix || !v->campos) { set_error("%s: NULL view tensor", who); return WS_E_INVALID; }
+    if (!g->means3D || (need_opacity && !g->opacities)) { set_error("%s: means3D and opacities are required", who); return WS_E_INVALID; }
+    const bool has_sh = g->shs != nullptr && g->M > 0, has_col = g->colors_precomp != nullptr;
+    if (has_sh == has_col) { // DGR rasterizer_impl.cu:243-246 / __init__.py:194-195
+        set_error("%s: provide exactly one of SHs or precomputed colors", who);
+        return WS_E_INVALID;
+    }
+    const bool has_sr = g->scales != nullptr && g->rotations != nullptr, has_cov = g->cov3D_precomp != nullptr;
+    if (has_sr == has_cov || ((g->scales != nullptr) != (g->rotations != nullptr))) {
+        set_error("%s: provide exactly one of scale/rotation pair or precomputed 3D covariance", who);
+        return WS_E_INVALID;
+    }
+    if (v->sh_degree < 0 || v->sh_degree > 3) { set_error("%s: sh_degree must be 0..3", who); return WS_E_INVALID; }
+    if (has_sh && (v->sh_degree + 1) * (v->sh_degree + 1) > g->M) {
+        set_error("%s: sh_degree %d needs %d coefficients, sh has %d", who, v->sh_degree,
+                  (v->sh_degree + 1) * (v->sh_degree + 1), g->M);
+        return WS_E_INVALID;
+    }
+    return WS_OK;
+}
+
+static int check_flash(const char *who, const ws_flash *fl, bool forward)
+{
+    if (!fl) return WS_OK;
+    if (fl->num_obj < 0 || !fl->gt_mask) { set_error("%s: flash needs gt_mask and num_obj >= 0", who); return WS_E_INVALID; }
+    if (forward && (!fl->out_contrib_num || !fl->used_count)) {
+        set_error("%s: flash forward needs out_contrib_num and used_count", who);
+        return WS_E_INVALID;
+    }
+    return WS_OK;
+}
+
+} // namespace ws
+
+using namespace ws;
+
+extern "C" int ws_abi_version(void) { return WS_ABI_VERSION; }
+extern "C" const char *ws_last_error(void) { return ws::g_err; }
+extern "C" int64_t ws_launch_count(void) { return ws::g_launch_count; }
+
+extern "C" size_t ws_geom_bytes(int32_t P)
+{
+    size_t b = 0;
+    GeomState::from(nullptr, (size_t)(P > 0 ? P : 0), &b);
+    return b + 256;
+}
+extern "C" size_t ws_image_bytes(int32_t width, int32_t height)
+{
+    size_t b = 0;
+    const size_t T = (size_t)((width + WS_BLOCK_X - 1) / WS_BLOCK_X) * ((height + WS_BLOCK_Y - 1) / WS_BLOCK_Y);
+    ImageState::from(nullptr, T, (size_t)width * height, &b);
+    return b + 256;
+}
+extern "C" size_t ws_binning_bytes(int64_t num_rendered, int32_t width, int32_t height)
+{
+    (void)width; (void)height;
+    size_t b = 0;
+    BinningState::from(nullptr, (size_t)(num_rendered > 0 ? num_rendered : 0), &b);
+    return b + 256;
+}
+
+extern "C" int64_t ws_forward_prepare(const ws_view *view, const ws_gaussians *g, int32_t *radii, void *geom,
+                                      size_t geom_bytes, const ws_flash *fl, ws_stream_t stream)
+{
+    int rc = check_view_gauss("ws_forward_prepare", view, g);
+    if (rc != WS_OK) return rc;
+    if (!radii || !geom) { set_error("ws_forward_prepare: NULL radii/geom"); return WS_E_INVALID; }
+    if (geom_bytes < ws_geom_bytes(g->P)) {
+        set_error("ws_forward_prepare: geom scratch too small (%zu < %zu)", geom_bytes, ws_geom_bytes(g->P));
+        return WS_E_SCRATCH;
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    GeomState gs = GeomState::from((char *)geom, (size_t)g->P);
+    rc = launch_preprocess(view, g, radii, gs, fl, st);
+    if (rc != WS_OK) return rc;
+    rc = launch_scan_blocks(g->P, gs, st, view->debug != 0);
+    if (rc != WS_OK) return rc;
+    uint32_t total = 0;
+    WS_CUDA_CHECK(cudaMemcpyAsync(&total, gs.total, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+    WS_CUDA_CHECK(cudaStreamSynchronize(st));
+    return (int64_t)total;
+}
+
+extern "C" int ws_forward_render(const ws_view *view, const ws_gaussians *g, const int32_t *radii, void *geom,
+                                 void *binning, size_t binning_bytes, void *image, size_t image_bytes,
+                                 int64_t num_rendered, float *out_color, float *out_depth, float *out_alpha,
+                                 const ws_flash *fl, ws_stream_t stream)
+{
+    int rc = check_view_gauss("ws_forward_render", view, g);
+    if (rc != WS_OK) return rc;
+    rc = check_flash("ws_forward_render", fl, true);
+    if (rc != WS_OK) return rc;
+    if (!radii || !geom || !image || !out_color || !out_depth || !out_alpha || num_rendered < 0 ||
+        (num_rendered > 0 && !binning)) {
+        set_error("ws_forward_render: NULL buffer");
+        return WS_E_INVALID;
+    }
+    const int W = view->image_width, H = view->image_height;
+    if (image_bytes < ws_image_bytes(W, H)) { set_error("ws_forward_render: image scratch too small"); return WS_E_SCRATCH; }
+    if (num_rendered > 0 && binning_bytes < ws_binning_bytes(num_rendered, W, H)) {
+        set_error("ws_forward_render: binning scratch too small (%zu < %zu)", binning_bytes,
+                  ws_binning_bytes(num_rendered, W, H));
+        return WS_E_SCRATCH;
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    const bool debug = view->debug != 0;
+    const int gx = (W + WS_BLOCK_X - 1) / WS_BLOCK_X, gy = (H + WS_BLOCK_Y - 1) / WS_BLOCK_Y;
+    const int T = gx * gy;
+    const size_t R = (size_t)num_rendered;
+    GeomState gs = GeomState::from((char *)geom, (size_t)g->P);
+    ImageState is = ImageState::from((char *)image, (size_t)T, (size_t)W * H);
+    BinningState bs = BinningState::from((char *)binning, R);
+    uint64_t *keys = nullptr;
+    uint32_t *vals = nullptr;
+    if (R > 0) {
+        rc = launch_emit_keys(g->P, W, H, radii, gs, bs.keys_a, bs.vals_a, st, debug);
+        if (rc != WS_OK) return rc;
+        const int end_bit = 32 + (int)get_higher_msb((uint32_t)T); // rasterizer_impl.cu:301-309
+        rc = launch_sort_pairs(R, bs.keys_a, bs.keys_b, bs.vals_a, bs.vals_b, end_bit, bs.sort, st, debug, &keys, &vals);
+        if (rc != WS_OK) return rc;
+    }
+    rc = launch_ranges_pack(R, T, keys, vals, gs, bs, is, st, debug);
+    if (rc != WS_OK) return rc;
+    return launch_render_fwd(view, g->P, gs, bs, is, out_color, out_depth, out_alpha, fl, st);
+}
+
+extern "C" int ws_backward(const ws_view *view, const ws_gaussians *g, const int32_t *radii, void *geom,
+                           void *binning, void *image, int64_t num_rendered, const float *out_alpha,
+                           const float *dL_dcolor, const float *dL_ddepth, const float *dL_dalpha,
+                           const ws_grads *gr, const ws_flash *fl, ws_stream_t stream)
+{
+    int rc = check_view_gauss("ws_backward", view, g, false); // opacity lives in the forward's geometry state
+    if (rc != WS_OK) return rc;
+    rc = check_flash("ws_backward", fl, false);
+    if (rc != WS_OK) return rc;
+    if (!radii || !geom || !image || !out_alpha || !dL_dcolor || !dL_ddepth || !dL_dalpha || !gr ||
+        (num_rendered > 0 && !binning)) {
+        set_error("ws_backward: NULL buffer");
+        return WS_E_INVALID;
+    }
+    if (!gr->dL_dmeans2D || !gr->dL_dcolors || !gr->dL_dopacity || !gr->dL_dmeans3D || !gr->dL_dcov3D ||
+        (g->shs && g->M > 0 && !gr->dL_dsh) || (g->scales && (!gr->dL_dscales || !gr->dL_drotations))) {
+        set_error("ws_backward: NULL gradient tensor");
+        return WS_E_INVALID;
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    const int W = view->image_width, H = view->image_height;
+    const int T = ((W + WS_BLOCK_X - 1) / WS_BLOCK_X) * ((H + WS_BLOCK_Y - 1) / WS_BLOCK_Y);
+    GeomState gs = GeomState::from((char *)geom, (size_t)g->P);
+    ImageState is = ImageState::from((char *)image, (size_t)T, (size_t)W * H);
+    BinningState bs = BinningState::from((char *)binning, (size_t)num_rendered);
+    rc = launch_render_bwd(view, g->P, gs, bs, is, out_alpha, dL_dcolor, dL_ddepth, dL_dalpha, fl, st);
+    if (rc != WS_OK) return rc;
+    return launch_preprocess_bwd(view, g, radii, gs, gr, st);
+}
+
+namespace ws {
+__global__ void unpack_geom(int P, int what, const float4 *__restrict__ g0, const float4 *__restrict__ g1,
+                            const float4 *__restrict__ g2, float *__restrict__ dst)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= P) return;
+    const float4 a = g0[i], b = g1[i], c = g2[i];
+    if (what == 0) dst[i] = b.z;                                              // depths
+    else if (what == 1) { dst[2 * i] = a.x; dst[2 * i + 1] = a.y; }          // means2D
+    else if (what == 2) { dst[4 * i] = a.z; dst[4 * i + 1] = a.w; dst[4 * i + 2] = b.x; dst[4 * i + 3] = b.y; }
+    else { dst[3 * i] = c.x; dst[3 * i + 1] = c.y; dst[3 * i + 2] = c.z; }   // rgb
+}
+} // namespace ws
+
+extern "C" int64_t ws_debug_fetch(const char *name, int32_t P, int32_t width, int32_t height, int64_t num_rendered,
+                                  void *geom, void *binning, void *image, void *dst, size_t dst_bytes,
+                                  ws_stream_t stream)
+{
+    if (!name || !dst) { set_error("ws_debug_fetch: NULL"); return WS_E_INVALID; }
+    cudaStream_t st = (cudaStream_t)stream;
+    const int T = ((width + WS_BLOCK_X - 1) / WS_BLOCK_X) * ((height + WS_BLOCK_Y - 1) / WS_BLOCK_Y);
+    const size_t R = (size_t)num_rendered;
+    GeomState gs = GeomState::from((char *)geom, (size_t)P);
+    int what = -1;
+    size_t need = 0;
+    if (!strcmp(name, "depths")) { what = 0; need = 4 * (size_t)P; }
+    else if (!strcmp(name, "means2D")) { what = 1; need = 8 * (size_t)P; }
+    else if (!strcmp(name, "conic_opacity")) { what = 2; need = 16 * (size_t)P; }
+    else if (!strcmp(name, "rgb")) { what = 3; need = 12 * (size_t)P; }
+    if (what >= 0) {
+        // only rows of visible Gaussians are meaningful (the reference leaves the rest stale too)
+        if (dst_bytes < need) { set_error("ws_debug_fetch: dst too small"); return WS_E_SCRATCH; }
+        WS_CUDA_CHECK(cudaMemsetAsync(dst, 0, need, st));
+        ws::unpack_geom<<<(P + 255) / 256, 256, 0, st>>>(P, what, gs.g0, gs.g1, gs.g2, (float *)dst);
+        WS_LAUNCH_CHECK(st, false);
+        return (int64_t)need;
+    }
+    const void *src = nullptr;
+    if (!strcmp(name, "tiles_touched")) { src = gs.tiles_touched; need = 4 * (size_t)P; }
+    else if (!strcmp(name, "ranges") || !strcmp(name, "n_contrib")) {
+        ImageState is = ImageState::from((char *)image, (size_t)T, (size_t)width * height);
+        if (!strcmp(name, "ranges")) { src = is.ranges; need = 8 * (size_t)T; }
+        else { src = is.n_contrib; need = 4 * (size_t)width * height; }
+    } else if (!strcmp(name, "point_list_keys") || !strcmp(name, "point_list")) {
+        if (R == 0) return 0;
+        BinningState bs = BinningState::from((char *)binning, R);
+        // the sorted pairs end in the "a" buffers after an even number of passes, else in "b"
+        const int end_bit = 32 + (int)ws::get_higher_msb((uint32_t)T);
+        const int npass = (end_bit + 7) / 8;
+        const bool in_b = (npass & 1) != 0;
+        if (!strcmp(name, "point_list_keys")) { src = in_b ? bs.keys_b : bs.keys_a; need = 8 * R; }
+        else { src = in_b ? bs.vals_b : bs.vals_a; need = 4 * R; }
+    } else {
+        set_error("ws_debug_fetch: unknown array '%s'", name);
+        return WS_E_INVALID;
+    }
+    if (dst_bytes < need) { set_error("ws_debug_fetch: dst too small"); return WS_E_SCRATCH; }
+    WS_CUDA_CHECK(cudaMemcpyAsync(dst, src, need, cudaMemcpyDeviceToDevice, st));
+    return (int64_t)need;
+}

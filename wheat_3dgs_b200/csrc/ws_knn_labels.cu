@@ -1,0 +1,243 @@
+// ws_knn_labels.cu
+//   ws_knn_dist2           simple-knn distCUDA2 (KNN/simple_knn.cu:186-222): bbox(points U origin),
+//                          30-bit Morton codes, stable sort, 1024-point boxes, pruned 3-NN search.
+//                          The reference copies the bbox to the host twice (:197,:200); here it stays
+//                          on the device, so the call is fully asynchronous.
+//   ws_multi_instance_opt  run_3d_seg.py:54-72 fused into one pass over the vote matrix (the
+//                          reference loops over labels in Python, a handful of torch kernels each).
+#include <float.h>
+#include "ws_common.cuh"
+
+namespace ws {
+
+struct MinMax { float minn[3], maxx[3]; };
+
+__global__ void __launch_bounds__(256) knn_bbox_partial(int P, const float *__restrict__ pts, float *__restrict__ part)
+{
+    float mn[3] = {0.f, 0.f, 0.f}, mx[3] = {0.f, 0.f, 0.f}; // init = {0,0,0}, simple_knn.cu:192
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < P; i += gridDim.x * blockDim.x)
+#pragma unroll
+        for (int k = 0; k < 3; k++) {
+            const float v = pts[3 * (size_t)i + k];
+            mn[k] = fminf(mn[k], v);
+            mx[k] = fmaxf(mx[k], v);
+        }
+    __shared__ float s[8][6];
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            mn[k] = fminf(mn[k], __shfl_xor_sync(0xffffffffu, mn[k], o));
+            mx[k] = fmaxf(mx[k], __shfl_xor_sync(0xffffffffu, mx[k], o));
+        }
+    }
+    if ((threadIdx.x & 31) == 0)
+        for (int k = 0; k < 3; k++) { s[threadIdx.x >> 5][k] = mn[k]; s[threadIdx.x >> 5][3 + k] = mx[k]; }
+    __syncthreads();
+    if (threadIdx.x < 6) {
+        float r = s[0][threadIdx.x];
+        for (int w = 1; w < 8; w++) r = threadIdx.x < 3 ? fminf(r, s[w][threadIdx.x]) : fmaxf(r, s[w][threadIdx.x]);
+        part[blockIdx.x * 6 + threadIdx.x] = r;
+    }
+}
+__global__ void knn_bbox_final(int nblk, const float *__restrict__ part, float *__restrict__ mm)
+{
+    const int k = threadIdx.x;
+    if (k >= 6) return;
+    float r = 0.f;
+    for (int b = 0; b < nblk; b++) r = k < 3 ? fminf(r, part[b * 6 + k]) : fmaxf(r, part[b * 6 + k]);
+    mm[k] = r;
+}
+
+__device__ __forceinline__ uint32_t prep_morton(uint32_t x) // simple_knn.cu:37-44
+{
+    x = (x | (x << 16)) & 0x030000FF;
+    x = (x | (x << 8)) & 0x0300F00F;
+    x = (x | (x << 4)) & 0x030C30C3;
+    x = (x | (x << 2)) & 0x09249249;
+    return x;
+}
+
+__global__ void knn_morton(int P, const float *__restrict__ pts, const float *__restrict__ mm,
+                           uint64_t *__restrict__ keys, uint32_t *__restrict__ vals)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= P) return;
+    uint32_t c[3];
+#pragma unroll
+    for (int k = 0; k < 3; k++) { // simple_knn.cu:46-62
+        const float t = __fmul_rn(__fdiv_rn(__fadd_rn(pts[3 * (size_t)i + k], -mm[k]), __fadd_rn(mm[3 + k], -mm[k])), 1023.0f);
+        c[k] = prep_morton(__float2uint_rz(t));
+    }
+    keys[i] = (uint64_t)(c[0] | (c[1] << 1) | (c[2] << 2));
+    vals[i] = (uint32_t)i;
+}
+
+// simple_knn.cu:79-118, one CTA of 1024 per box
+__global__ void __launch_bounds__(1024) knn_box_minmax(int P, const float *__restrict__ pts,
+                                                       const uint32_t *__restrict__ idx, MinMax *__restrict__ boxes)
+{
+    const int i = blockIdx.x * 1024 + threadIdx.x;
+    float mn[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, mx[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
+    if (i < P) {
+        const uint32_t g = idx[i];
+#pragma unroll
+        for (int k = 0; k < 3; k++) mn[k] = mx[k] = pts[3 * (size_t)g + k];
+    }
+    __shared__ float s[32][6];
+#pragma unroll
+    for (int k = 0; k < 3; k++)
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            mn[k] = fminf(mn[k], __shfl_xor_sync(0xffffffffu, mn[k], o));
+            mx[k] = fmaxf(mx[k], __shfl_xor_sync(0xffffffffu, mx[k], o));
+        }
+    if ((threadIdx.x & 31) == 0)
+        for (int k = 0; k < 3; k++) { s[threadIdx.x >> 5][k] = mn[k]; s[threadIdx.x >> 5][3 + k] = mx[k]; }
+    __syncthreads();
+    if (threadIdx.x < 6) {
+        float r = s[0][threadIdx.x];
+        for (int w = 1; w < 32; w++) r = threadIdx.x < 3 ? fminf(r, s[w][threadIdx.x]) : fmaxf(r, s[w][threadIdx.x]);
+        if (threadIdx.x < 3) boxes[blockIdx.x].minn[threadIdx.x] = r;
+        else boxes[blockIdx.x].maxx[threadIdx.x - 3] = r;
+    }
+}
+
+__device__ __forceinline__ void update3(const float px, const float py, const float pz, const float *q, float *knn)
+{
+    const float dx = __fadd_rn(q[0], -px), dy = __fadd_rn(q[1], -py), dz = __fadd_rn(q[2], -pz);
+    float dist = __fmaf_rn(dz, dz, __fmaf_rn(dx, dx, __fmul_rn(dy, dy))); // contraction as in the reference SASS
+#pragma unroll
+    for (int j = 0; j < 3; j++)
+        if (knn[j] > dist) { const float t = knn[j]; knn[j] = dist; dist = t; }
+}
+
+// simple_knn.cu:148-184
+__global__ void __launch_bounds__(256) knn_box_mean_dist(int P, const float *__restrict__ pts,
+                                                         const uint32_t *__restrict__ idx,
+                                                         const MinMax *__restrict__ boxes, float *__restrict__ dists)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= P) return;
+    const uint32_t me = idx[i];
+    const float px = pts[3 * (size_t)me], py = pts[3 * (size_t)me + 1], pz = pts[3 * (size_t)me + 2];
+    float best[3] = {FLT_MAX, FLT_MAX, FLT_MAX};
+    for (int j = max(0, i - 3); j <= min(P - 1, i + 3); j++) {
+        if (j == i) continue;
+        update3(px, py, pz, pts + 3 * (size_t)idx[j], best);
+    }
+    const float reject = best[2];
+    best[0] = best[1] = best[2] = FLT_MAX;
+    const int nb = (P + 1023) / 1024;
+    for (int b = 0; b < nb; b++) {
+        const MinMax box = boxes[b];
+        float d[3] = {0.f, 0.f, 0.f};
+        const float pp[3] = {px, py, pz};
+#pragma unroll
+        for (int k = 0; k < 3; k++)
+            if (pp[k] < box.minn[k] || pp[k] > box.maxx[k])
+                d[k] = fminf(fabsf(__fadd_rn(pp[k], -box.minn[k])), fabsf(__fadd_rn(pp[k], -box.maxx[k])));
+        const float dist = __fmaf_rn(d[2], d[2], __fmaf_rn(d[0], d[0], __fmul_rn(d[1], d[1])));
+        if (dist > reject || dist > best[2]) continue;
+        const int end = min(P, (b + 1) * 1024);
+        for (int j = b * 1024; j < end; j++) {
+            if (j == i) continue;
+            update3(px, py, pz, pts + 3 * (size_t)idx[j], best);
+        }
+    }
+    dists[me] = __fdiv_rn(__fadd_rn(best[2], __fadd_rn(best[0], best[1])), 3.0f);
+}
+
+struct KnnScratch {
+    float *part, *mm;
+    uint64_t *keys_a, *keys_b;
+    uint32_t *vals_a, *vals_b;
+    MinMax *boxes;
+    SortScratch sort;
+    static KnnScratch from(char *p, size_t P, size_t *bytes)
+    {
+        KnnScratch s;
+        char *p0 = p;
+        s.part = carve<float>(p, 6 * 1024);
+        s.mm = carve<float>(p, 8);
+        s.keys_a = carve<uint64_t>(p, P + 64);
+        s.keys_b = carve<uint64_t>(p, P + 64);
+        s.vals_a = carve<uint32_t>(p, P + 64);
+        s.vals_b = carve<uint32_t>(p, P + 64);
+        s.boxes = carve<MinMax>(p, (P + 1023) / 1024 + 1);
+        s.sort = SortScratch::from(p, P);
+        if (bytes) *bytes = (size_t)(p - p0) + 256;
+        return s;
+    }
+};
+
+// multi_instance_opt: thread per Gaussian (column).  labels[i][j] = argmax over
+// normalize([sum_j - A_ij, A_ij]) with gamma on row 0; ties -> 0.
+__global__ void __launch_bounds__(256) multi_instance_opt_kernel(int rows, int P, const float *__restrict__ A,
+                                                                 float gamma, uint8_t *__restrict__ labels)
+{
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= P) return;
+    float sum = 0.f;
+    for (int i = 0; i < rows; i++) sum = __fadd_rn(sum, A[(size_t)i * P + j]);
+    for (int i = 0; i < rows; i++) {
+        const float a = A[(size_t)i * P + j];
+        const float rest = __fadd_rn(sum, -a);
+        float nrm = sqrtf(__fadd_rn(__fmul_rn(rest, rest), __fmul_rn(a, a)));
+        nrm = fmaxf(nrm, 1e-12f); // F.normalize eps
+        const float n0 = __fadd_rn(__fdiv_rn(rest, nrm), gamma), n1 = __fdiv_rn(a, nrm);
+        labels[(size_t)i * P + j] = n1 > n0 ? 1 : 0;
+    }
+}
+
+} // namespace ws
+
+using namespace ws;
+
+extern "C" size_t ws_knn_bytes(int32_t P)
+{
+    size_t b = 0;
+    KnnScratch::from(nullptr, (size_t)(P > 0 ? P : 0), &b);
+    return b + 256;
+}
+
+extern "C" int ws_knn_dist2(int32_t P, const float *points, float *mean_dists, void *scratch, size_t scratch_bytes,
+                            ws_stream_t stream)
+{
+    if (P < 0 || (P > 0 && (!points || !mean_dists || !scratch))) { set_error("ws_knn_dist2: bad arguments"); return WS_E_INVALID; }
+    if (P == 0) return WS_OK;
+    if (scratch_bytes < ws_knn_bytes(P)) { set_error("ws_knn_dist2: scratch too small"); return WS_E_SCRATCH; }
+    cudaStream_t st = (cudaStream_t)stream;
+    KnnScratch ks = KnnScratch::from((char *)scratch, (size_t)P, nullptr);
+    int nblk = (P + 256 * 8 - 1) / (256 * 8);
+    if (nblk > 1024) nblk = 1024;
+    knn_bbox_partial<<<nblk, 256, 0, st>>>(P, points, ks.part);
+    WS_LAUNCH_CHECK(st, false);
+    knn_bbox_final<<<1, 32, 0, st>>>(nblk, ks.part, ks.mm);
+    WS_LAUNCH_CHECK(st, false);
+    knn_morton<<<(P + 255) / 256, 256, 0, st>>>(P, points, ks.mm, ks.keys_a, ks.vals_a);
+    WS_LAUNCH_CHECK(st, false);
+    uint64_t *kf;
+    uint32_t *vf;
+    int rc = launch_sort_pairs((size_t)P, ks.keys_a, ks.keys_b, ks.vals_a, ks.vals_b, 32, ks.sort, st, false, &kf, &vf);
+    if (rc != WS_OK) return rc;
+    const int nb = (P + 1023) / 1024;
+    knn_box_minmax<<<nb, 1024, 0, st>>>(P, points, vf, ks.boxes);
+    WS_LAUNCH_CHECK(st, false);
+    knn_box_mean_dist<<<(P + 255) / 256, 256, 0, st>>>(P, points, vf, ks.boxes, mean_dists);
+    WS_LAUNCH_CHECK(st, false);
+    return WS_OK;
+}
+
+extern "C" int ws_multi_instance_opt(int32_t num_rows, int32_t P, const float *all_contrib, float gamma,
+                                     uint8_t *labels, ws_stream_t stream)
+{
+    if (num_rows < 0 || P < 0 || ((size_t)num_rows * P > 0 && (!all_contrib || !labels))) {
+        set_error("ws_multi_instance_opt: bad arguments");
+        return WS_E_INVALID;
+    }
+    if ((size_t)num_rows * P == 0) return WS_OK;
+    multi_instance_opt_kernel<<<(P + 255) / 256, 256, 0, (cudaStream_t)stream>>>(num_rows, P, all_contrib, gamma, labels);
+    WS_LAUNCH_CHECK((cudaStream_t)stream, false);
+    return WS_OK;
+}

@@ -1,0 +1,295 @@
+// ws_radix_sort.cu -- hand-written onesweep LSD radix sort of (u64 key, u32 value) pairs on key
+// bits [0, end_bit).  Replaces cub::DeviceRadixSort::SortPairs (DGR rasterizer_impl.cu:304-309;
+// KNN simple_knn.cu:211-214).  No CUB, no Thrust.
+//
+//   rs_histogram   one read of the keys -> global digit histograms of every pass at once
+//   rs_scan_hist   exclusive scan of each pass's 256 bins -> digit base offsets
+//   rs_onesweep    one launch per 8-bit pass: every CTA takes a tile of 256 x 12 keys (ticket
+//                  from an atomic counter so predecessors are always resident), ranks them in
+//                  shared memory, learns the number of equal digits in all earlier tiles by a
+//                  decoupled look-back over per-(tile,digit) status words, and scatters.
+//                  Keys and values are read once and written once per pass.
+//
+// Stability (needed for bit-exact parity of point_list: equal (tile,depth) keys must keep the
+// emission order = ascending Gaussian id).  Within a digit the output order is
+//   tile order (look-back prefix)  ->  warp order inside the tile (exclusive scan over the
+//   per-warp digit counters)  ->  item order inside the warp (warp-striped load: item i of
+//   lane l is element i*32 + l of the warp's segment, items ranked i-ascending, lanes by
+//   lanemask_lt).  That is exactly input order.
+//
+// Algorithmic HBM bytes: 8n (histogram) + passes * 24n (12 B read + 12 B written per pair).
+#include "ws_common.cuh"
+
+namespace ws {
+
+constexpr int RS_THREADS = 256;
+constexpr int RS_WARPS = RS_THREADS / 32;
+constexpr int RS_ITEMS = 12;
+constexpr int RS_TILE = RS_THREADS * RS_ITEMS; // 3072 pairs per CTA
+constexpr int RS_MAX_PASSES = 8;
+
+constexpr uint32_t RS_FLAG_AGG = 1u << 30; // tile aggregate available
+constexpr uint32_t RS_FLAG_INC = 2u << 30; // inclusive prefix available
+constexpr uint32_t RS_VAL_MASK = (1u << 30) - 1;
+
+size_t sort_tiles(size_t n) { return (n + RS_TILE - 1) / RS_TILE; }
+
+SortScratch SortScratch::from(char *&p, size_t n)
+{
+    SortScratch s;
+    s.hist = carve<uint32_t>(p, RS_MAX_PASSES * 256 + 64); // counters live right behind hist
+    s.counters = s.hist + RS_MAX_PASSES * 256;
+    size_t nt = sort_tiles(n);
+    s.status = carve<uint32_t>(p, (size_t)RS_MAX_PASSES * (nt ? nt : 1) * 256);
+    return s;
+}
+
+__global__ void __launch_bounds__(256) rs_histogram(const uint64_t *__restrict__ keys, size_t n, int end_bit,
+                                                    uint32_t *__restrict__ hist)
+{
+    __shared__ uint32_t sh[RS_MAX_PASSES * 256];
+    const int npass = (end_bit + 7) / 8;
+    for (int j = threadIdx.x; j < npass * 256; j += blockDim.x) sh[j] = 0;
+    __syncthreads();
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        const uint64_t key = keys[i];
+        for (int p = 0; p < npass; p++) {
+            const int bits = min(8, end_bit - 8 * p);
+            const uint32_t d = (uint32_t)(key >> (8 * p)) & ((1u << bits) - 1u);
+            atomicAdd(&sh[p * 256 + d], 1u);
+        }
+    }
+    __syncthreads();
+    for (int j = threadIdx.x; j < npass * 256; j += blockDim.x) {
+        const uint32_t c = sh[j];
+        if (c) atomicAdd(&hist[j], c);
+    }
+}
+
+// exclusive scan over 256 values held one per thread (256 threads); returns the exclusive prefix
+__device__ __forceinline__ uint32_t block_excl_scan_256(uint32_t v, uint32_t *s_w /*[8]*/)
+{
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    uint32_t inc = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        uint32_t n = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += n;
+    }
+    if (lane == 31) s_w[w] = inc;
+    __syncthreads();
+    uint32_t base = 0;
+#pragma unroll
+    for (int k = 0; k < RS_WARPS; k++)
+        if (k < w) base += s_w[k];
+    __syncthreads();
+    return base + inc - v;
+}
+
+__global__ void __launch_bounds__(256) rs_scan_hist(uint32_t *__restrict__ hist)
+{
+    __shared__ uint32_t s_w[RS_WARPS];
+    uint32_t *h = hist + blockIdx.x * 256;
+    const uint32_t v = h[threadIdx.x];
+    h[threadIdx.x] = block_excl_scan_256(v, s_w);
+}
+
+__device__ __forceinline__ uint32_t ld_relaxed(const uint32_t *p)
+{
+    uint32_t v;
+    asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_relaxed(uint32_t *p, uint32_t v)
+{
+    asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+__global__ void __launch_bounds__(RS_THREADS)
+rs_onesweep(const uint64_t *__restrict__ keys_in, uint64_t *__restrict__ keys_out,
+            const uint32_t *__restrict__ vals_in, uint32_t *__restrict__ vals_out, size_t n, int shift,
+            int bits, const uint32_t *__restrict__ bins, uint32_t *__restrict__ counter,
+            uint32_t *__restrict__ status)
+{
+    __shared__ uint64_t s_keys[RS_TILE];          // 24 KB
+    __shared__ uint32_t s_vals[RS_TILE];          // 12 KB
+    __shared__ uint32_t s_whist[RS_WARPS][256];   //  8 KB
+    __shared__ uint32_t s_dstart[256];
+    __shared__ uint32_t s_goff[256];
+    __shared__ uint32_t s_w[RS_WARPS];
+    __shared__ uint32_t s_tile;
+
+    const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+    const uint32_t mask = (1u << bits) - 1u;
+    const uint32_t lt_mask = (1u << lane) - 1u;
+
+    if (tid == 0) s_tile = atomicAdd(counter, 1u);
+#pragma unroll
+    for (int k = 0; k < RS_WARPS; k++) s_whist[k][tid] = 0;
+    __syncthreads();
+    const uint32_t tile = s_tile;
+    const size_t base = (size_t)tile * RS_TILE;
+    const size_t seg = base + (size_t)w * (RS_ITEMS * 32);
+
+    uint64_t key[RS_ITEMS];
+    uint32_t val[RS_ITEMS];
+    uint32_t rank[RS_ITEMS];
+#pragma unroll
+    for (int i = 0; i < RS_ITEMS; i++) {
+        const size_t idx = seg + (size_t)i * 32 + lane;
+        const bool valid = idx < n;
+        key[i] = valid ? keys_in[idx] : ~0ull;
+        val[i] = valid ? vals_in[idx] : 0u;
+    }
+
+    // ---- rank inside the warp, item by item (stable) ----
+#pragma unroll
+    for (int i = 0; i < RS_ITEMS; i++) {
+        const bool valid = (seg + (size_t)i * 32 + lane) < n;
+        const uint32_t d = valid ? ((uint32_t)(key[i] >> shift) & mask) : 0x100u;
+        const uint32_t peers = __match_any_sync(0xffffffffu, d);
+        uint32_t pre = 0;
+        if (valid) pre = s_whist[w][d];
+        __syncwarp();
+        if (valid && (peers & lt_mask) == 0) s_whist[w][d] = pre + __popc(peers);
+        __syncwarp();
+        rank[i] = pre + __popc(peers & lt_mask);
+    }
+    __syncthreads();
+
+    // ---- thread d owns digit d: exclusive scan over the warps, tile count, look-back ----
+    uint32_t run = 0;
+#pragma unroll
+    for (int k = 0; k < RS_WARPS; k++) {
+        const uint32_t c = s_whist[k][tid];
+        s_whist[k][tid] = run;
+        run += c;
+    }
+    uint32_t *my_status = status + (size_t)tile * 256 + tid;
+    uint32_t excl = 0;
+    if (tile == 0) {
+        st_relaxed(my_status, run | RS_FLAG_INC);
+    } else {
+        st_relaxed(my_status, run | RS_FLAG_AGG);
+        int look = (int)tile - 1;
+        while (true) {
+            const uint32_t *ps = status + (size_t)look * 256 + tid;
+            uint32_t v = ld_relaxed(ps);
+            while ((v & (RS_FLAG_AGG | RS_FLAG_INC)) == 0) {
+                __nanosleep(20);
+                v = ld_relaxed(ps);
+            }
+            excl += v & RS_VAL_MASK;
+            if (v & RS_FLAG_INC) break;
+            look--;
+        }
+        st_relaxed(my_status, ((excl + run) & RS_VAL_MASK) | RS_FLAG_INC);
+    }
+    const uint32_t dstart = block_excl_scan_256(run, s_w); // contains __syncthreads
+    s_dstart[tid] = dstart;
+    s_goff[tid] = bins[tid] + excl - dstart;
+    __syncthreads();
+
+    // ---- scatter into shared memory in sorted order ----
+#pragma unroll
+    for (int i = 0; i < RS_ITEMS; i++) {
+        const bool valid = (seg + (size_t)i * 32 + lane) < n;
+        if (valid) {
+            const uint32_t d = (uint32_t)(key[i] >> shift) & mask;
+            const uint32_t pos = s_dstart[d] + s_whist[w][d] + rank[i];
+            s_keys[pos] = key[i];
+            s_vals[pos] = val[i];
+        }
+    }
+    __syncthreads();
+
+    // ---- write out: consecutive positions of one digit are consecutive in global memory ----
+    const uint32_t ntile = (uint32_t)min((size_t)RS_TILE, n - base);
+#pragma unroll
+    for (int j = 0; j < RS_ITEMS; j++) {
+        const uint32_t p = tid + j * RS_THREADS;
+        if (p < ntile) {
+            const uint64_t k = s_keys[p];
+            const uint32_t d = (uint32_t)(k >> shift) & mask;
+            const size_t dst = (size_t)(s_goff[d] + p);
+            keys_out[dst] = k;
+            vals_out[dst] = s_vals[p];
+        }
+    }
+}
+
+int launch_sort_pairs(size_t n, uint64_t *keys_in, uint64_t *keys_out, uint32_t *vals_in,
+                      uint32_t *vals_out, int end_bit, SortScratch &ss, cudaStream_t st, bool debug,
+                      uint64_t **keys_final, uint32_t **vals_final)
+{
+    *keys_final = keys_in;
+    *vals_final = vals_in;
+    if (n == 0) return WS_OK;
+    if (n >= (size_t)RS_VAL_MASK) {
+        set_error("radix sort: %zu pairs exceed the 2^30-1 limit of the look-back status words", n);
+        return WS_E_UNSUPPORTED;
+    }
+    if (end_bit < 1 || end_bit > 64) {
+        set_error("radix sort: end_bit %d out of range", end_bit);
+        return WS_E_INVALID;
+    }
+    const int npass = (end_bit + 7) / 8;
+    const size_t nt = sort_tiles(n);
+    WS_CUDA_CHECK(cudaMemsetAsync(ss.hist, 0, (RS_MAX_PASSES * 256 + 64) * sizeof(uint32_t), st));
+    WS_CUDA_CHECK(cudaMemsetAsync(ss.status, 0, (size_t)npass * nt * 256 * sizeof(uint32_t), st));
+    int hb = (int)((n + 256 * 16 - 1) / (256 * 16));
+    if (hb > 148 * 8) hb = 148 * 8;
+    rs_histogram<<<hb, 256, 0, st>>>(keys_in, n, end_bit, ss.hist);
+    WS_LAUNCH_CHECK(st, debug);
+    rs_scan_hist<<<npass, 256, 0, st>>>(ss.hist);
+    WS_LAUNCH_CHECK(st, debug);
+    uint64_t *ki = keys_in, *ko = keys_out;
+    uint32_t *vi = vals_in, *vo = vals_out;
+    for (int p = 0; p < npass; p++) {
+        const int bits = end_bit - 8 * p < 8 ? end_bit - 8 * p : 8;
+        rs_onesweep<<<(unsigned)nt, RS_THREADS, 0, st>>>(ki, ko, vi, vo, n, 8 * p, bits, ss.hist + p * 256,
+                                                         ss.counters + p, ss.status + (size_t)p * nt * 256);
+        WS_LAUNCH_CHECK(st, debug);
+        uint64_t *tk = ki; ki = ko; ko = tk;
+        uint32_t *tv = vi; vi = vo; vo = tv;
+    }
+    *keys_final = ki;
+    *vals_final = vi;
+    return WS_OK;
+}
+
+} // namespace ws
+
+extern "C" size_t ws_sort_bytes(int64_t n)
+{
+    char *p = nullptr;
+    ws::SortScratch::from(p, (size_t)(n > 0 ? n : 0));
+    return (size_t)p + 512;
+}
+
+extern "C" int ws_sort_pairs_u64(int64_t n, uint64_t *keys_in, uint64_t *keys_out, uint32_t *vals_in,
+                                 uint32_t *vals_out, int32_t end_bit, void *scratch, size_t scratch_bytes,
+                                 ws_stream_t stream)
+{
+    if (n < 0 || (n > 0 && (!keys_in || !keys_out || !vals_in || !vals_out || !scratch))) {
+        ws::set_error("ws_sort_pairs_u64: bad arguments");
+        return WS_E_INVALID;
+    }
+    if (scratch_bytes < ws_sort_bytes(n)) {
+        ws::set_error("ws_sort_pairs_u64: scratch too small (%zu < %zu)", scratch_bytes, ws_sort_bytes(n));
+        return WS_E_SCRATCH;
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    char *p = (char *)scratch;
+    ws::SortScratch ss = ws::SortScratch::from(p, (size_t)n);
+    uint64_t *kf;
+    uint32_t *vf;
+    int rc = ws::launch_sort_pairs((size_t)n, keys_in, keys_out, vals_in, vals_out, end_bit, ss, st, false, &kf, &vf);
+    if (rc != WS_OK) return rc;
+    if (n > 0 && kf != keys_out) {
+        WS_CUDA_CHECK(cudaMemcpyAsync(keys_out, kf, (size_t)n * 8, cudaMemcpyDeviceToDevice, st));
+        WS_CUDA_CHECK(cudaMemcpyAsync(vals_out, vf, (size_t)n * 4, cudaMemcpyDeviceToDevice, st));
+    }
+    return WS_OK;
+}

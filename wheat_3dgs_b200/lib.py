@@ -1,0 +1,115 @@
+"""ctypes binding of libwheatsplat.so (the C ABI in include/wheatsplat.h).
+
+The library is the product: there is no CPU or PyTorch fallback.  If the shared object is
+missing or a symbol is absent, import fails loudly.
+"""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libwheatsplat.so")
+
+WS_ABI_VERSION = 1
+
+# every symbol include/wheatsplat.h declares (tests check the library exports all of them)
+SYMBOLS = [
+    "ws_abi_version", "ws_last_error", "ws_geom_bytes", "ws_image_bytes", "ws_binning_bytes",
+    "ws_forward_prepare", "ws_forward_render", "ws_backward", "ws_mark_visible", "ws_knn_bytes",
+    "ws_knn_dist2", "ws_multi_instance_opt", "ws_sort_bytes", "ws_sort_pairs_u64", "ws_debug_fetch",
+    "ws_launch_count",
+]
+
+
+class WsView(C.Structure):
+    _fields_ = [("image_height", C.c_int32), ("image_width", C.c_int32), ("tanfovx", C.c_float),
+                ("tanfovy", C.c_float), ("scale_modifier", C.c_float), ("sh_degree", C.c_int32),
+                ("prefiltered", C.c_int32), ("debug", C.c_int32), ("bg", C.c_void_p),
+                ("viewmatrix", C.c_void_p), ("projmatrix", C.c_void_p), ("campos", C.c_void_p)]
+
+
+class WsGaussians(C.Structure):
+    _fields_ = [("P", C.c_int32), ("M", C.c_int32), ("means3D", C.c_void_p), ("shs", C.c_void_p),
+                ("colors_precomp", C.c_void_p), ("opacities", C.c_void_p), ("scales", C.c_void_p),
+                ("rotations", C.c_void_p), ("cov3D_precomp", C.c_void_p)]
+
+
+class WsFlash(C.Structure):
+    _fields_ = [("num_obj", C.c_int32), ("gt_mask", C.c_void_p), ("unique_label", C.c_void_p),
+                ("out_contrib_num", C.c_void_p), ("used_count", C.c_void_p), ("image_xys", C.c_void_p),
+                ("gs_depth", C.c_void_p)]
+
+
+class WsGrads(C.Structure):
+    _fields_ = [("dL_dmeans2D", C.c_void_p), ("dL_dcolors", C.c_void_p), ("dL_dopacity", C.c_void_p),
+                ("dL_dmeans3D", C.c_void_p), ("dL_dcov3D", C.c_void_p), ("dL_dsh", C.c_void_p),
+                ("dL_dscales", C.c_void_p), ("dL_drotations", C.c_void_p)]
+
+
+_lib = None
+
+
+def load():
+    """Loads libwheatsplat.so (building it first if nvcc and the sources are there and the
+    library is stale or missing)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    try:
+        from . import build as _build
+        _build.build()
+    except Exception as e:  # noqa: BLE001 - surfaced below if the library is unusable
+        if not os.path.exists(LIB_PATH):
+            raise ImportError(
+                "libwheatsplat.so is missing and could not be built (%s). This package has no "
+                "CPU/PyTorch fallback: build it with `python -m wheat_3dgs_b200.build`." % e)
+    lib = C.CDLL(LIB_PATH)
+    for s in SYMBOLS:
+        if not hasattr(lib, s):
+            raise ImportError("libwheatsplat.so does not export %s (stale build?)" % s)
+    vp, i32, i64, sz, f32 = C.c_void_p, C.c_int32, C.c_int64, C.c_size_t, C.c_float
+    lib.ws_abi_version.restype = C.c_int
+    lib.ws_last_error.restype = C.c_char_p
+    lib.ws_launch_count.restype = i64
+    lib.ws_geom_bytes.restype = sz
+    lib.ws_geom_bytes.argtypes = [i32]
+    lib.ws_image_bytes.restype = sz
+    lib.ws_image_bytes.argtypes = [i32, i32]
+    lib.ws_binning_bytes.restype = sz
+    lib.ws_binning_bytes.argtypes = [i64, i32, i32]
+    lib.ws_forward_prepare.restype = i64
+    lib.ws_forward_prepare.argtypes = [C.POINTER(WsView), C.POINTER(WsGaussians), vp, vp, sz,
+                                       C.POINTER(WsFlash), vp]
+    lib.ws_forward_render.restype = C.c_int
+    lib.ws_forward_render.argtypes = [C.POINTER(WsView), C.POINTER(WsGaussians), vp, vp, vp, sz, vp, sz, i64,
+                                      vp, vp, vp, C.POINTER(WsFlash), vp]
+    lib.ws_backward.restype = C.c_int
+    lib.ws_backward.argtypes = [C.POINTER(WsView), C.POINTER(WsGaussians), vp, vp, vp, vp, i64, vp, vp, vp, vp,
+                                C.POINTER(WsGrads), C.POINTER(WsFlash), vp]
+    lib.ws_mark_visible.restype = C.c_int
+    lib.ws_mark_visible.argtypes = [i32, vp, vp, vp, vp, vp]
+    lib.ws_knn_bytes.restype = sz
+    lib.ws_knn_bytes.argtypes = [i32]
+    lib.ws_knn_dist2.restype = C.c_int
+    lib.ws_knn_dist2.argtypes = [i32, vp, vp, vp, sz, vp]
+    lib.ws_multi_instance_opt.restype = C.c_int
+    lib.ws_multi_instance_opt.argtypes = [i32, i32, vp, f32, vp, vp]
+    lib.ws_sort_bytes.restype = sz
+    lib.ws_sort_bytes.argtypes = [i64]
+    lib.ws_sort_pairs_u64.restype = C.c_int
+    lib.ws_sort_pairs_u64.argtypes = [i64, vp, vp, vp, vp, i32, vp, sz, vp]
+    lib.ws_debug_fetch.restype = i64
+    lib.ws_debug_fetch.argtypes = [C.c_char_p, i32, i32, i32, i64, vp, vp, vp, vp, sz, vp]
+    if lib.ws_abi_version() != WS_ABI_VERSION:
+        raise ImportError("libwheatsplat.so ABI %d != expected %d" % (lib.ws_abi_version(), WS_ABI_VERSION))
+    _lib = lib
+    return lib
+
+
+def last_error():
+    return load().ws_last_error().decode("utf-8", "replace")
+
+
+def check(rc, what):
+    if rc < 0:
+        raise RuntimeError("%s failed (%d): %s" % (what, rc, last_error()))
+    return rc

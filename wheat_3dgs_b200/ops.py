@@ -1,0 +1,306 @@
+"""Torch-level operators over the C ABI, with the names, argument order and return tuples of the
+pybind modules they replace:
+
+  rasterize_gaussians / rasterize_gaussians_backward / mark_visible
+      = diff_gaussian_rasterization._C (reference submodules/diff-gaussian-rasterization/
+        rasterize_points.h:18-70, ext.cpp:15-19)
+  flash_rasterize_gaussians / flash_rasterize_gaussians_backward
+      = flashsplat_rasterization._C (reference submodules/flashsplat-rasterization/
+        rasterize_points.h:18-46)
+  distCUDA2 = simple_knn._C.distCUDA2 (reference submodules/simple-knn/spatial.cu:15-26)
+  multi_instance_opt = run_3d_seg.py:54-72 on the device
+
+PyTorch is plumbing here (allocation, streams); all compute is in libwheatsplat.so.  Optional
+inputs follow the reference convention: an empty tensor means "not provided"
+(diff_gaussian_rasterization/__init__.py:200-210).
+"""
+import ctypes as C
+
+import torch
+
+from . import lib as _lib
+from .lib import WsFlash, WsGaussians, WsGrads, WsView
+
+
+def _ptr(t):
+    if t is None or t.numel() == 0:
+        return None
+    return t.data_ptr()
+
+
+def _f32c(t, name):
+    if t is None or t.numel() == 0:
+        return None
+    if not t.is_cuda:
+        raise RuntimeError("%s must be a CUDA tensor (wheat_3dgs_b200 has no CPU path)" % name)
+    if t.dtype != torch.float32:
+        t = t.float()
+    return t.contiguous()
+
+
+def _stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+class _Call:
+    """Marshals one rasterizer call: keeps the contiguous tensors alive and builds the structs."""
+
+    def __init__(self, bg, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp,
+                 viewmatrix, projmatrix, tanfovx, tanfovy, image_height, image_width, sh, degree, campos,
+                 prefiltered, debug):
+        if means3D.dim() != 2 or means3D.size(1) != 3:  # DGR rasterize_points.cu:57-59
+            raise RuntimeError("means3D must have dimensions (num_points, 3)")
+        self.P = means3D.size(0)
+        self.H, self.W = int(image_height), int(image_width)
+        self.keep = dict(
+            bg=_f32c(bg, "bg"), means3D=_f32c(means3D, "means3D"), colors=_f32c(colors, "colors_precomp"),
+            opacity=_f32c(opacity, "opacities"), scales=_f32c(scales, "scales"),
+            rotations=_f32c(rotations, "rotations"), cov3D=_f32c(cov3D_precomp, "cov3D_precomp"),
+            view=_f32c(viewmatrix, "viewmatrix"), proj=_f32c(projmatrix, "projmatrix"), sh=_f32c(sh, "sh"),
+            campos=_f32c(campos, "campos"))
+        k = self.keep
+        self.M = 0 if k["sh"] is None else k["sh"].size(1)  # DGR rasterize_points.cu:85-89
+        self.device = means3D.device
+        self.view = WsView(self.H, self.W, float(tanfovx), float(tanfovy), float(scale_modifier), int(degree),
+                           int(bool(prefiltered)), int(bool(debug)), _ptr(k["bg"]), _ptr(k["view"]),
+                           _ptr(k["proj"]), _ptr(k["campos"]))
+        self.gauss = WsGaussians(self.P, self.M, _ptr(k["means3D"]), _ptr(k["sh"]), _ptr(k["colors"]),
+                                 _ptr(k["opacity"]), _ptr(k["scales"]), _ptr(k["rotations"]), _ptr(k["cov3D"]))
+
+
+def _forward(call, flash):
+    """Shared forward: returns (R, color, depth, alpha, radii, geom, binning, image)."""
+    L = _lib.load()
+    dev, P, H, W = call.device, call.P, call.H, call.W
+    f32 = dict(dtype=torch.float32, device=dev)
+    u8 = dict(dtype=torch.uint8, device=dev)
+    color = torch.empty((3, H, W), **f32)
+    depth = torch.empty((1, H, W), **f32)
+    alpha = torch.empty((1, H, W), **f32)
+    radii = torch.empty((P,), dtype=torch.int32, device=dev)
+    geom = torch.empty((L.ws_geom_bytes(P),), **u8)
+    image = torch.empty((L.ws_image_bytes(W, H),), **u8)
+    fl = C.byref(flash) if flash is not None else None
+    with torch.cuda.device(dev):
+        st = _stream()
+        R = _lib.check(L.ws_forward_prepare(C.byref(call.view), C.byref(call.gauss), radii.data_ptr(),
+                                            geom.data_ptr(), geom.numel(), fl, st), "ws_forward_prepare")
+        binning = torch.empty((L.ws_binning_bytes(R, W, H) if R > 0 else 0,), **u8)
+        _lib.check(L.ws_forward_render(C.byref(call.view), C.byref(call.gauss), radii.data_ptr(), geom.data_ptr(),
+                                       _ptr(binning), binning.numel(), image.data_ptr(), image.numel(), R,
+                                       color.data_ptr(), depth.data_ptr(), alpha.data_ptr(), fl, st),
+                   "ws_forward_render")
+    return R, color, depth, alpha, radii, geom, binning, image
+
+
+def rasterize_gaussians(bg, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp,
+                        viewmatrix, projmatrix, tanfovx, tanfovy, image_height, image_width, sh, degree,
+                        campos, prefiltered, debug):
+    """= _C.rasterize_gaussians (DGR rasterize_points.cu:35-119).
+    Returns (num_rendered, color[3,H,W], depth[1,H,W], alpha[1,H,W], radii[P] int32, geomBuffer,
+    binningBuffer, imgBuffer)."""
+    call = _Call(bg, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp, viewmatrix,
+                 projmatrix, tanfovx, tanfovy, image_height, image_width, sh, degree, campos, prefiltered, debug)
+    if call.P == 0:  # DGR rasterize_points.cu:82: nothing is launched, outputs stay zero
+        dev = means3D.device
+        z = lambda *s: torch.zeros(s, dtype=torch.float32, device=dev)
+        e = torch.empty((0,), dtype=torch.uint8, device=dev)
+        return 0, z(3, call.H, call.W), z(1, call.H, call.W), z(1, call.H, call.W), \
+            torch.zeros((0,), dtype=torch.int32, device=dev), e, e.clone(), e.clone()
+    return _forward(call, None)
+
+
+def _backward(call, radii, geom, binning, image, R, alpha, dL_dcolor, dL_ddepth, dL_dalpha, flash, bucket=None):
+    L = _lib.load()
+    dev, P, M = call.device, call.P, call.M
+    has_sr = call.keep["scales"] is not None
+    # one flat allocation: [means3D 3 | means2D 3 | sh 3M | opacity 1 | scales 3 | rot 4 | colors 3 | cov3D 6]
+    # The first 14+3M floats per Gaussian are exactly the training-time gradient set, contiguous,
+    # so a data-parallel trainer can all-reduce them as ONE bucket (wheat_3dgs_b200/dist.py).
+    sizes = [3, 3, 3 * M, 1, 3, 4, 3, 6]
+    total = sum(sizes) * P
+    if bucket is None:
+        bucket = torch.empty((total,), dtype=torch.float32, device=dev)
+    elif bucket.numel() < total or bucket.dtype != torch.float32 or not bucket.is_contiguous():
+        raise RuntimeError("gradient bucket must be a contiguous float32 tensor of >= %d elements" % total)
+    views, off = [], 0
+    for s in sizes:
+        views.append(bucket[off:off + s * P])
+        off += s * P
+    g_means3D, g_means2D, g_sh, g_opac, g_scales, g_rot, g_colors, g_cov = views
+    grads = WsGrads(g_means2D.data_ptr(), g_colors.data_ptr(), g_opac.data_ptr(), g_means3D.data_ptr(),
+                    g_cov.data_ptr(), g_sh.data_ptr() if M > 0 else None,
+                    g_scales.data_ptr() if has_sr else None, g_rot.data_ptr() if has_sr else None)
+    dc, dd, da = _f32c(dL_dcolor, "dL_dout_color"), _f32c(dL_ddepth, "dL_dout_depth"), _f32c(dL_dalpha, "dL_dout_alpha")
+    al = _f32c(alpha, "alphas")
+    fl = C.byref(flash) if flash is not None else None
+    with torch.cuda.device(dev):
+        _lib.check(L.ws_backward(C.byref(call.view), C.byref(call.gauss), radii.data_ptr(), geom.data_ptr(),
+                                 _ptr(binning), image.data_ptr(), int(R), al.data_ptr(), dc.data_ptr(),
+                                 dd.data_ptr(), da.data_ptr(), C.byref(grads), fl, _stream()), "ws_backward")
+    if not has_sr:
+        g_scales.zero_()
+        g_rot.zero_()
+    return (g_means2D.view(P, 3), g_colors.view(P, 3), g_opac.view(P, 1), g_means3D.view(P, 3), g_cov.view(P, 6),
+            g_sh.view(P, M, 3), g_scales.view(P, 3), g_rot.view(P, 4))
+
+
+def rasterize_gaussians_backward(bg, means3D, radii, colors, scales, rotations, scale_modifier, cov3D_precomp,
+                                 viewmatrix, projmatrix, tanfovx, tanfovy, dL_dout_color, dL_dout_depth,
+                                 dL_dout_alpha, sh, degree, campos, geomBuffer, R, binningBuffer, imageBuffer,
+                                 alphas, debug, _bucket=None):
+    """= _C.rasterize_gaussians_backward (DGR rasterize_points.cu:121-208).  Returns
+    (dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations)."""
+    H, W = dL_dout_color.size(1), dL_dout_color.size(2)
+    P = means3D.size(0)
+    M = sh.size(1) if sh is not None and sh.numel() != 0 else 0
+    if P == 0:
+        z = lambda *s: torch.zeros(s, dtype=torch.float32, device=means3D.device)
+        return z(0, 3), z(0, 3), z(0, 1), z(0, 3), z(0, 6), z(0, M, 3), z(0, 3), z(0, 4)
+    # opacities are not needed by the backward (they live in the forward's geometry state)
+    call = _Call(bg, means3D, colors, None, scales, rotations, scale_modifier, cov3D_precomp,
+                 viewmatrix, projmatrix, tanfovx, tanfovy, H, W, sh, degree, campos, False, debug)
+    return _backward(call, radii, geomBuffer, binningBuffer, imageBuffer, R, alphas, dL_dout_color,
+                     dL_dout_depth, dL_dout_alpha, None, _bucket)
+
+
+def mark_visible(means3D, viewmatrix, projmatrix):
+    """= _C.mark_visible (DGR rasterize_points.cu:210-229) -> bool[P]."""
+    L = _lib.load()
+    m, v, pm = _f32c(means3D, "means3D"), _f32c(viewmatrix, "viewmatrix"), _f32c(projmatrix, "projmatrix")
+    P = means3D.size(0)
+    present = torch.zeros((P,), dtype=torch.uint8, device=means3D.device)
+    if P:
+        with torch.cuda.device(means3D.device):
+            _lib.check(L.ws_mark_visible(P, m.data_ptr(), v.data_ptr(), _ptr(pm), present.data_ptr(), _stream()),
+                       "ws_mark_visible")
+    return present.view(torch.bool)
+
+
+def flash_rasterize_gaussians(gt_mask, unique_label, bg, means3D, colors, opacity, scales, rotations,
+                              scale_modifier, cov3D_precomp, viewmatrix, projmatrix, tanfovx, tanfovy,
+                              image_height, image_width, sh, degree, campos, prefiltered, num_obj, debug,
+                              used_count_out=None):
+    """= flashsplat _C.rasterize_gaussians (FSR rasterize_points.cu:36-131).  Returns the 12-tuple
+    (num_rendered, color, depth, alpha, radii, geomBuffer, binningBuffer, imgBuffer, out_contrib_num,
+    used_count, image_xys, gs_depth).  `used_count_out`: optional persistent [num_obj+1,P] buffer the
+    votes are ACCUMULATED into (one buffer across views instead of a 2 GB zero-fill per view)."""
+    call = _Call(bg, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp, viewmatrix,
+                 projmatrix, tanfovx, tanfovy, image_height, image_width, sh, degree, campos, prefiltered, debug)
+    dev, P, H, W = means3D.device, call.P, call.H, call.W
+    contrib = torch.empty((1, H, W), dtype=torch.int32, device=dev) if P else \
+        torch.zeros((1, H, W), dtype=torch.int32, device=dev)
+    if used_count_out is None:
+        used = torch.zeros((num_obj + 1, P), dtype=torch.float32, device=dev)
+    else:
+        used = used_count_out
+        if used.shape != (num_obj + 1, P) or used.dtype != torch.float32 or not used.is_contiguous():
+            raise RuntimeError("used_count_out must be contiguous float32 [num_obj+1, P]")
+    xys = torch.full((2, P), -1.0, dtype=torch.float32, device=dev)   # FSR rasterize_points.cu:77
+    gsd = torch.full((P,), -0.1, dtype=torch.float32, device=dev)     # FSR rasterize_points.cu:78
+    if P == 0:
+        z = lambda *s: torch.zeros(s, dtype=torch.float32, device=dev)
+        e = torch.empty((0,), dtype=torch.uint8, device=dev)
+        return (0, z(3, H, W), z(1, H, W), z(1, H, W), torch.zeros((0,), dtype=torch.int32, device=dev), e,
+                e.clone(), e.clone(), contrib, used, xys, gsd)
+    gm = _f32c(gt_mask, "gt_mask")
+    if gm.numel() != H * W:
+        raise RuntimeError("gt_mask must have image_height*image_width elements")
+    ul = None
+    if unique_label is not None and unique_label.numel() != 0:
+        ul = unique_label.to(device=dev, dtype=torch.int32).contiguous()
+        if ul.numel() != P:
+            raise RuntimeError("unique_label must have P elements")
+    flash = WsFlash(int(num_obj), gm.data_ptr(), _ptr(ul), contrib.data_ptr(), used.data_ptr(), xys.data_ptr(),
+                    gsd.data_ptr())
+    call.keep["flash"] = (gm, ul)
+    R, color, depth, alpha, radii, geom, binning, image = _forward(call, flash)
+    return R, color, depth, alpha, radii, geom, binning, image, contrib, used, xys, gsd
+
+
+def flash_rasterize_gaussians_backward(gt_mask, unique_label, bg, means3D, radii, colors, scales, rotations,
+                                       scale_modifier, cov3D_precomp, viewmatrix, projmatrix, tanfovx, tanfovy,
+                                       dL_dout_color, dL_dout_depth, dL_dout_alpha, sh, degree, campos,
+                                       geomBuffer, R, binningBuffer, imageBuffer, alphas, debug):
+    """= flashsplat _C.rasterize_gaussians_backward (FSR rasterize_points.cu:134-226)."""
+    H, W = dL_dout_color.size(1), dL_dout_color.size(2)
+    P = means3D.size(0)
+    M = sh.size(1) if sh is not None and sh.numel() != 0 else 0
+    if P == 0:
+        z = lambda *s: torch.zeros(s, dtype=torch.float32, device=means3D.device)
+        return z(0, 3), z(0, 3), z(0, 1), z(0, 3), z(0, 6), z(0, M, 3), z(0, 3), z(0, 4)
+    call = _Call(bg, means3D, colors, None, scales, rotations, scale_modifier, cov3D_precomp,
+                 viewmatrix, projmatrix, tanfovx, tanfovy, H, W, sh, degree, campos, False, debug)
+    gm = _f32c(gt_mask, "gt_mask")
+    ul = None
+    if unique_label is not None and unique_label.numel() != 0:
+        ul = unique_label.to(device=means3D.device, dtype=torch.int32).contiguous()
+    flash = WsFlash(0, gm.data_ptr(), _ptr(ul), None, None, None, None)
+    return _backward(call, radii, geomBuffer, binningBuffer, imageBuffer, R, alphas, dL_dout_color,
+                     dL_dout_depth, dL_dout_alpha, flash)
+
+
+def distCUDA2(points):
+    """= simple_knn._C.distCUDA2: mean squared distance to the 3 nearest neighbours, float[P]."""
+    L = _lib.load()
+    p = _f32c(points, "points")
+    P = points.size(0)
+    means = torch.zeros((P,), dtype=torch.float32, device=points.device)
+    if P:
+        scratch = torch.empty((L.ws_knn_bytes(P),), dtype=torch.uint8, device=points.device)
+        with torch.cuda.device(points.device):
+            _lib.check(L.ws_knn_dist2(P, p.data_ptr(), means.data_ptr(), scratch.data_ptr(), scratch.numel(),
+                                      _stream()), "ws_knn_dist2")
+    return means
+
+
+def multi_instance_opt(all_contrib, gamma=0.0):
+    """Device version of run_3d_seg.py:54-72: float[num_obj+1, P] votes -> bool[num_obj+1, P]."""
+    L = _lib.load()
+    a = _f32c(all_contrib, "all_contrib")
+    rows, P = all_contrib.shape
+    out = torch.zeros((rows, P), dtype=torch.uint8, device=all_contrib.device)
+    if rows * P:
+        with torch.cuda.device(all_contrib.device):
+            _lib.check(L.ws_multi_instance_opt(rows, P, a.data_ptr(), float(gamma), out.data_ptr(), _stream()),
+                       "ws_multi_instance_opt")
+    return out.view(torch.bool)
+
+
+def sort_pairs(keys, vals, end_bit):
+    """Stable radix sort of (int64-viewed-as-u64 keys, int32-viewed-as-u32 vals) on bits [0,end_bit)."""
+    L = _lib.load()
+    n = keys.numel()
+    k_in, v_in = keys.clone().contiguous(), vals.clone().contiguous()
+    k_out, v_out = torch.empty_like(k_in), torch.empty_like(v_in)
+    if n:
+        scratch = torch.empty((L.ws_sort_bytes(n),), dtype=torch.uint8, device=keys.device)
+        with torch.cuda.device(keys.device):
+            _lib.check(L.ws_sort_pairs_u64(n, k_in.data_ptr(), k_out.data_ptr(), v_in.data_ptr(), v_out.data_ptr(),
+                                           int(end_bit), scratch.data_ptr(), scratch.numel(), _stream()),
+                       "ws_sort_pairs_u64")
+    return k_out, v_out
+
+
+_FETCH = {"depths": (torch.float32, lambda P, T, HW, R: (P,)), "means2D": (torch.float32, lambda P, T, HW, R: (P, 2)),
+          "conic_opacity": (torch.float32, lambda P, T, HW, R: (P, 4)), "rgb": (torch.float32, lambda P, T, HW, R: (P, 3)),
+          "tiles_touched": (torch.int32, lambda P, T, HW, R: (P,)), "point_list_keys": (torch.int64, lambda P, T, HW, R: (R,)),
+          "point_list": (torch.int32, lambda P, T, HW, R: (R,)), "ranges": (torch.int32, lambda P, T, HW, R: (T, 2)),
+          "n_contrib": (torch.int32, lambda P, T, HW, R: (HW,))}
+
+
+def debug_fetch(name, P, W, H, R, geom, binning, image):
+    """Internal arrays of a finished forward, for parity tests (see ws_debug_fetch)."""
+    L = _lib.load()
+    dt, shp = _FETCH[name]
+    T = ((W + 15) // 16) * ((H + 15) // 16)
+    out = torch.zeros(shp(P, T, H * W, R), dtype=dt, device=geom.device)
+    if out.numel():
+        with torch.cuda.device(geom.device):
+            _lib.check(L.ws_debug_fetch(name.encode(), P, W, H, R, geom.data_ptr(), _ptr(binning), image.data_ptr(),
+                                        out.data_ptr(), out.numel() * out.element_size(), _stream()), "ws_debug_fetch")
+    return out
+
+
+def launch_count():
+    return int(_lib.load().ws_launch_count())
