@@ -173,6 +173,24 @@ int64_t ws_debug_fetch(const char *name, int32_t P, int32_t width, int32_t heigh
 /* Number of kernels this library launched since load (bench.py's gpu_launches counter). */
 int64_t ws_launch_count(void);
 
+/* Stage timing for bench.py's roofline figures.  While enabled, ws_forward_prepare /
+ * ws_forward_render / ws_backward bracket every stage with CUDA events recorded on the caller's
+ * stream.  ws_prof_read synchronises on the recorded events, adds the elapsed milliseconds and the
+ * number of brackets per stage into ms[WS_PROF_NSTAGES] / calls[WS_PROF_NSTAGES] and forgets them.
+ * Stages: 0 preprocess, 1 scan, 2 emit_keys, 3 sort (histogram + onesweep passes), 4 ranges_pack,
+ * 5 render_fwd, 6 render_bwd, 7 preprocess_bwd. */
+#define WS_PROF_NSTAGES 8
+void ws_prof_enable(int32_t on);
+int ws_prof_read(double *ms, int64_t *calls);
+const char *ws_prof_stage_name(int32_t stage);
+
+/* Work counters of a finished forward, for the blend kernels' flop figures:
+ * counts[0] = N_eval = sum over pixels of n_contrib (pairs traversed up to the last contributor),
+ * counts[1] = N_contrib = pairs among those with power <= 0 and alpha >= 1/255.
+ * counts is device uint64[2], zeroed by the call. */
+int ws_debug_count_pairs(int32_t width, int32_t height, void *binning, void *image, int64_t num_rendered,
+                         uint64_t *counts, ws_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -44,7 +44,7 @@ class RefRasterizer:
         H, W = cam["image_height"], cam["image_width"]
         shs = g.get("shs")
         M = 0 if shs is None else shs.shape[1]
-        o = outputs or {}
+        o = outputs if outputs is not None else {}
         f32 = dict(dtype=torch.float32, device=dev)
         o.setdefault("color", torch.empty((3, H, W), **f32))
         o.setdefault("depth", torch.empty((1, H, W), **f32))
@@ -77,7 +77,7 @@ class RefRasterizer:
         g, cam, P, M = L["g"], L["cam"], L["P"], L["M"]
         dev = g["means3D"].device
         f32 = dict(dtype=torch.float32, device=dev)
-        gr = grads or {}
+        gr = grads if grads is not None else {}
         for name, shape in (("dL_dmeans2D", (P, 3)), ("dL_dconic", (P, 2, 2)), ("dL_dopacity", (P, 1)),
                             ("dL_dcolors", (P, 3)), ("dL_ddepths", (P, 1)), ("dL_dmeans3D", (P, 3)),
                             ("dL_dcov3D", (P, 6)), ("dL_dsh", (P, M, 3)), ("dL_dscales", (P, 3)),

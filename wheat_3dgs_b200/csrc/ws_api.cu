@@ -2,6 +2,8 @@
 // scratch carving and stage sequencing.  No device memory is allocated here.
 #include <stdarg.h>
 #include <string.h>
+#include <mutex>
+#include <vector>
 #include "ws_common.cuh"
 
 namespace ws {
@@ -16,6 +18,40 @@ void set_error(const char *fmt, ...)
     vsnprintf(g_err, sizeof(g_err), fmt, ap);
     va_end(ap);
 }
+
+// ---- stage timing (ws_prof_*): CUDA events on the caller's stream around every stage ----
+static bool g_prof = false;
+struct ProfRec { int stage; cudaEvent_t a, b; };
+static std::vector<ProfRec> g_prof_recs;
+static std::vector<cudaEvent_t> g_prof_free;
+static std::mutex g_prof_mu;
+
+static cudaEvent_t prof_event()
+{
+    cudaEvent_t e = nullptr;
+    if (!g_prof_free.empty()) { e = g_prof_free.back(); g_prof_free.pop_back(); }
+    else cudaEventCreate(&e);
+    return e;
+}
+
+struct ProfScope {
+    int stage; cudaStream_t st; cudaEvent_t a = nullptr;
+    ProfScope(int stage_, cudaStream_t st_) : stage(stage_), st(st_)
+    {
+        if (!g_prof) return;
+        std::lock_guard<std::mutex> lk(g_prof_mu);
+        a = prof_event();
+        cudaEventRecord(a, st);
+    }
+    ~ProfScope()
+    {
+        if (!a) return;
+        std::lock_guard<std::mutex> lk(g_prof_mu);
+        cudaEvent_t b = prof_event();
+        cudaEventRecord(b, st);
+        g_prof_recs.push_back({stage, a, b});
+    }
+};
 
 // DGR rasterizer_impl.cu:35-50
 static uint32_t get_higher_msb(uint32_t n)
@@ -74,6 +110,30 @@ extern "C" int ws_abi_version(void) { return WS_ABI_VERSION; }
 extern "C" const char *ws_last_error(void) { return ws::g_err; }
 extern "C" int64_t ws_launch_count(void) { return ws::g_launch_count; }
 
+extern "C" void ws_prof_enable(int32_t on) { ws::g_prof = on != 0; }
+extern "C" const char *ws_prof_stage_name(int32_t stage)
+{
+    static const char *names[WS_PROF_NSTAGES] = {"preprocess", "scan", "emit_keys", "sort", "ranges_pack",
+                                                 "render_fwd", "render_bwd", "preprocess_bwd"};
+    return (stage >= 0 && stage < WS_PROF_NSTAGES) ? names[stage] : "?";
+}
+extern "C" int ws_prof_read(double *ms, int64_t *calls)
+{
+    if (!ms || !calls) { set_error("ws_prof_read: NULL"); return WS_E_INVALID; }
+    std::lock_guard<std::mutex> lk(ws::g_prof_mu);
+    for (auto &r : ws::g_prof_recs) {
+        float t = 0.f;
+        WS_CUDA_CHECK(cudaEventSynchronize(r.b));
+        WS_CUDA_CHECK(cudaEventElapsedTime(&t, r.a, r.b));
+        ms[r.stage] += (double)t;
+        calls[r.stage] += 1;
+        ws::g_prof_free.push_back(r.a);
+        ws::g_prof_free.push_back(r.b);
+    }
+    ws::g_prof_recs.clear();
+    return WS_OK;
+}
+
 extern "C" size_t ws_geom_bytes(int32_t P)
 {
     size_t b = 0;
@@ -107,9 +167,9 @@ extern "C" int64_t ws_forward_prepare(const ws_view *view, const ws_gaussians *g
     }
     cudaStream_t st = (cudaStream_t)stream;
     GeomState gs = GeomState::from((char *)geom, (size_t)g->P);
-    rc = launch_preprocess(view, g, radii, gs, fl, st);
+    { ProfScope ps(0, st); rc = launch_preprocess(view, g, radii, gs, fl, st); }
     if (rc != WS_OK) return rc;
-    rc = launch_scan_blocks(g->P, gs, st, view->debug != 0);
+    { ProfScope ps(1, st); rc = launch_scan_blocks(g->P, gs, st, view->debug != 0); }
     if (rc != WS_OK) return rc;
     uint32_t total = 0;
     WS_CUDA_CHECK(cudaMemcpyAsync(&total, gs.total, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
@@ -149,15 +209,16 @@ extern "C" int ws_forward_render(const ws_view *view, const ws_gaussians *g, con
     uint64_t *keys = nullptr;
     uint32_t *vals = nullptr;
     if (R > 0) {
-        rc = launch_emit_keys(g->P, W, H, radii, gs, bs.keys_a, bs.vals_a, st, debug);
+        { ProfScope ps(2, st); rc = launch_emit_keys(g->P, W, H, radii, gs, bs.keys_a, bs.vals_a, st, debug); }
         if (rc != WS_OK) return rc;
         const int end_bit = 32 + (int)get_higher_msb((uint32_t)T); // rasterizer_impl.cu:301-309
-        rc = launch_sort_pairs(R, bs.keys_a, bs.keys_b, bs.vals_a, bs.vals_b, end_bit, bs.sort, st, debug, &keys, &vals);
+        { ProfScope ps(3, st); rc = launch_sort_pairs(R, bs.keys_a, bs.keys_b, bs.vals_a, bs.vals_b, end_bit, bs.sort, st, debug, &keys, &vals); }
         if (rc != WS_OK) return rc;
     }
-    rc = launch_ranges_pack(R, T, keys, vals, gs, bs, is, st, debug);
+    { ProfScope ps(4, st); rc = launch_ranges_pack(R, T, keys, vals, gs, bs, is, st, debug); }
     if (rc != WS_OK) return rc;
-    return launch_render_fwd(view, g->P, gs, bs, is, out_color, out_depth, out_alpha, fl, st);
+    { ProfScope ps(5, st); rc = launch_render_fwd(view, g->P, gs, bs, is, out_color, out_depth, out_alpha, fl, st); }
+    return rc;
 }
 
 extern "C" int ws_backward(const ws_view *view, const ws_gaussians *g, const int32_t *radii, void *geom,
@@ -185,9 +246,10 @@ extern "C" int ws_backward(const ws_view *view, const ws_gaussians *g, const int
     GeomState gs = GeomState::from((char *)geom, (size_t)g->P);
     ImageState is = ImageState::from((char *)image, (size_t)T, (size_t)W * H);
     BinningState bs = BinningState::from((char *)binning, (size_t)num_rendered);
-    rc = launch_render_bwd(view, g->P, gs, bs, is, out_alpha, dL_dcolor, dL_ddepth, dL_dalpha, fl, st);
+    { ProfScope ps(6, st); rc = launch_render_bwd(view, g->P, gs, bs, is, out_alpha, dL_dcolor, dL_ddepth, dL_dalpha, fl, st); }
     if (rc != WS_OK) return rc;
-    return launch_preprocess_bwd(view, g, radii, gs, gr, st);
+    { ProfScope ps(7, st); rc = launch_preprocess_bwd(view, g, radii, gs, gr, st); }
+    return rc;
 }
 
 namespace ws {
@@ -203,6 +265,54 @@ __global__ void unpack_geom(int P, int what, const float4 *__restrict__ g0, cons
     else { dst[3 * i] = c.x; dst[3 * i + 1] = c.y; dst[3 * i + 2] = c.z; }   // rgb
 }
 } // namespace ws
+
+namespace ws {
+// one thread per pixel: re-walks its tile's packed records up to the pixel's last contributor
+__global__ void __launch_bounds__(256) count_pairs(int W, int H, const uint2 *__restrict__ ranges,
+                                                   const uint32_t *__restrict__ n_contrib,
+                                                   const float4 *__restrict__ q0, const float4 *__restrict__ q1,
+                                                   unsigned long long *__restrict__ counts)
+{
+    const int px = blockIdx.x * WS_BLOCK_X + (threadIdx.x & 15), py = blockIdx.y * WS_BLOCK_Y + (threadIdx.x >> 4);
+    unsigned long long ne = 0, nc = 0;
+    if (px < W && py < H) {
+        const uint2 range = ranges[blockIdx.y * gridDim.x + blockIdx.x];
+        const uint32_t last = n_contrib[(size_t)py * W + px];
+        ne = last;
+        for (uint32_t k = 0; k < last; k++) {
+            const float4 a = q0[range.x + k], q = q1[range.x + k];
+            const float dx = a.x - (float)px, dy = a.y - (float)py;
+            const float power = -0.5f * (a.z * dx * dx + q.x * dy * dy) - a.w * dx * dy;
+            if (power > 0.0f) continue;
+            if (fminf(0.99f, q.y * expf(power)) < 1.0f / 255.0f) continue;
+            nc++;
+        }
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+        ne += __shfl_xor_sync(0xffffffffu, ne, o);
+        nc += __shfl_xor_sync(0xffffffffu, nc, o);
+    }
+    if ((threadIdx.x & 31) == 0) { atomicAdd(counts, ne); atomicAdd(counts + 1, nc); }
+}
+} // namespace ws
+
+extern "C" int ws_debug_count_pairs(int32_t width, int32_t height, void *binning, void *image, int64_t num_rendered,
+                                    uint64_t *counts, ws_stream_t stream)
+{
+    if (!image || !counts || width <= 0 || height <= 0 || (num_rendered > 0 && !binning)) {
+        set_error("ws_debug_count_pairs: bad arguments");
+        return WS_E_INVALID;
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    const int gx = (width + WS_BLOCK_X - 1) / WS_BLOCK_X, gy = (height + WS_BLOCK_Y - 1) / WS_BLOCK_Y;
+    ImageState is = ImageState::from((char *)image, (size_t)gx * gy, (size_t)width * height);
+    BinningState bs = BinningState::from((char *)binning, (size_t)num_rendered);
+    WS_CUDA_CHECK(cudaMemsetAsync(counts, 0, 16, st));
+    ws::count_pairs<<<dim3(gx, gy), 256, 0, st>>>(width, height, is.ranges, is.n_contrib, bs.q0, bs.q1,
+                                                 (unsigned long long *)counts);
+    WS_LAUNCH_CHECK(st, false);
+    return WS_OK;
+}
 
 extern "C" int64_t ws_debug_fetch(const char *name, int32_t P, int32_t width, int32_t height, int64_t num_rendered,
                                   void *geom, void *binning, void *image, void *dst, size_t dst_bytes,

@@ -1,0 +1,128 @@
+"""View / frame / mask sharding across the GPUs of one box (one process per GPU).
+
+The reference is single-GPU (utils/general_utils.py:133 pins cuda:0) and does one view per
+iteration (train_vanilla_3dgs.py:65).  The hot path shards by independent units with ONE
+exchange step:
+
+  training views   rank r takes views r, r+N, ... of the epoch; every rank holds all Gaussians;
+                   the per-Gaussian gradients of the N views of a step are summed with one NCCL
+                   all_reduce over the flat bucket ops._backward() writes
+                   ([means3D 3 | means2D 3 | sh 3M | opacity 1 | scales 3 | rotations 4] x P floats,
+                   the training-time gradient set, contiguous).
+  label votes      (view, mask) units round-robin; used_count[(num_obj+1) x P] accumulated locally
+                   across the rank's views in one persistent buffer, all-reduced ONCE at the end
+                   (render_360.py:62-69 / run_3d_seg.py:97 add per-view counts on the host).
+  orbit frames     frames r::N, no exchange (render_360, utils/wheatgs_helper.py:282).
+
+Works with the `nccl` backend on CUDA tensors and with `gloo` on CPU tensors (the CPU tests run
+the host logic at world_size 2 under gloo).
+"""
+import os
+
+import torch
+import torch.distributed as dist
+
+TRAIN_GRAD_FLOATS = lambda M: 3 + 3 + 3 * M + 1 + 3 + 4  # noqa: E731  per Gaussian
+
+
+def init_from_env(backend=None):
+    """Initialises torch.distributed from RANK / WORLD_SIZE / MASTER_* (torchrun).  Returns
+    (rank, world_size, local_rank).  Single-process runs return (0, 1, 0) without a group."""
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world > 1 and not dist.is_initialized():
+        if backend is None:
+            backend = "nccl" if torch.cuda.is_available() else "gloo"
+        if backend == "nccl":
+            torch.cuda.set_device(local)
+            dist.init_process_group(backend, device_id=torch.device("cuda", local))
+        else:
+            dist.init_process_group(backend)
+    return rank, world, local
+
+
+def world_size():
+    return dist.get_world_size() if dist.is_initialized() else 1
+
+
+def shard(units, rank, world):
+    """Round-robin partition of independent units (views, frames, (view, mask) pairs)."""
+    return list(units)[rank::world]
+
+
+def shard_counts(n_units, world):
+    """Units per rank of shard(range(n_units), r, world) for every r."""
+    return [len(range(r, n_units, world)) for r in range(world)]
+
+
+def train_bucket_numel(P, M):
+    return TRAIN_GRAD_FLOATS(M) * P
+
+
+def full_bucket_numel(P, M):
+    """ops._backward() layout: the training set followed by [colors 3 | cov3D 6]."""
+    return (TRAIN_GRAD_FLOATS(M) + 9) * P
+
+
+def split_bucket(bucket, P, M):
+    """Views into the flat gradient bucket, keyed like the reference's returned gradients."""
+    sizes = (("dL_dmeans3D", 3), ("dL_dmeans2D", 3), ("dL_dsh", 3 * M), ("dL_dopacity", 1), ("dL_dscales", 3),
+             ("dL_drotations", 4), ("dL_dcolors", 3), ("dL_dcov3D", 6))
+    out, off = {}, 0
+    for name, s in sizes:
+        out[name] = bucket[off:off + s * P]
+        off += s * P
+    out["dL_dsh"] = out["dL_dsh"].view(P, M, 3)
+    for name, s in sizes:
+        if name != "dL_dsh":
+            out[name] = out[name].view(P, s)
+    return out
+
+
+def allreduce_train_grads(bucket, P, M, async_op=False):
+    """SUM over ranks of the training gradient set (62*P floats at SH degree 3) in ONE collective."""
+    if world_size() == 1:
+        return None
+    return dist.all_reduce(bucket[:train_bucket_numel(P, M)], op=dist.ReduceOp.SUM, async_op=async_op)
+
+
+def allreduce_votes(used_count, async_op=False):
+    """SUM over ranks of the label-vote accumulator used_count[(num_obj+1), P]."""
+    if world_size() == 1:
+        return None
+    return dist.all_reduce(used_count, op=dist.ReduceOp.SUM, async_op=async_op)
+
+
+def allreduce_densify_stats(xyz_gradient_accum, denom, max_radii2D):
+    """Densification statistics (scene/gaussian_model.py:461-463): SUM, SUM, MAX."""
+    if world_size() == 1:
+        return
+    dist.all_reduce(xyz_gradient_accum, op=dist.ReduceOp.SUM)
+    dist.all_reduce(denom, op=dist.ReduceOp.SUM)
+    dist.all_reduce(max_radii2D, op=dist.ReduceOp.MAX)
+
+
+def gather_frames(frame, n_frames, rank, world):
+    """Frames rendered as shard(range(n_frames)) gathered in frame order on rank 0 (None elsewhere)."""
+    if world == 1:
+        return [frame] if not isinstance(frame, list) else frame
+    mine = frame if isinstance(frame, list) else [frame]
+    out = [None] * world
+    dist.all_gather_object(out, [f.cpu() for f in mine])
+    if rank != 0:
+        return None
+    frames = [None] * n_frames
+    for r in range(world):
+        for k, f in zip(range(r, n_frames, world), out[r]):
+            frames[k] = f
+    return frames
+
+
+def max_over_ranks(value, device):
+    """Max over ranks of a python float (timings are reported as the slowest rank's)."""
+    if world_size() == 1:
+        return float(value)
+    t = torch.tensor([float(value)], dtype=torch.float64, device=device)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())

@@ -16,8 +16,9 @@ SYMBOLS = [
     "ws_abi_version", "ws_last_error", "ws_geom_bytes", "ws_image_bytes", "ws_binning_bytes",
     "ws_forward_prepare", "ws_forward_render", "ws_backward", "ws_mark_visible", "ws_knn_bytes",
     "ws_knn_dist2", "ws_multi_instance_opt", "ws_sort_bytes", "ws_sort_pairs_u64", "ws_debug_fetch",
-    "ws_launch_count",
+    "ws_launch_count", "ws_prof_enable", "ws_prof_read", "ws_prof_stage_name", "ws_debug_count_pairs",
 ]
+WS_PROF_NSTAGES = 8
 
 
 class WsView(C.Structure):
@@ -99,6 +100,14 @@ def load():
     lib.ws_sort_pairs_u64.argtypes = [i64, vp, vp, vp, vp, i32, vp, sz, vp]
     lib.ws_debug_fetch.restype = i64
     lib.ws_debug_fetch.argtypes = [C.c_char_p, i32, i32, i32, i64, vp, vp, vp, vp, sz, vp]
+    lib.ws_prof_enable.restype = None
+    lib.ws_prof_enable.argtypes = [i32]
+    lib.ws_prof_read.restype = C.c_int
+    lib.ws_prof_read.argtypes = [C.POINTER(C.c_double), C.POINTER(i64)]
+    lib.ws_prof_stage_name.restype = C.c_char_p
+    lib.ws_prof_stage_name.argtypes = [i32]
+    lib.ws_debug_count_pairs.restype = C.c_int
+    lib.ws_debug_count_pairs.argtypes = [i32, i32, vp, vp, i64, vp, vp]
     if lib.ws_abi_version() != WS_ABI_VERSION:
         raise ImportError("libwheatsplat.so ABI %d != expected %d" % (lib.ws_abi_version(), WS_ABI_VERSION))
     _lib = lib

@@ -304,3 +304,29 @@ def debug_fetch(name, P, W, H, R, geom, binning, image):
 
 def launch_count():
     return int(_lib.load().ws_launch_count())
+
+
+def prof_enable(on):
+    """Stage timing with CUDA events inside the library (bench.py's roofline leg)."""
+    _lib.load().ws_prof_enable(1 if on else 0)
+
+
+def prof_read():
+    """{stage name: (total ms, brackets)} accumulated since the last read."""
+    L = _lib.load()
+    n = _lib.WS_PROF_NSTAGES
+    ms = (C.c_double * n)()
+    calls = (C.c_int64 * n)()
+    _lib.check(L.ws_prof_read(ms, calls), "ws_prof_read")
+    return {L.ws_prof_stage_name(i).decode(): (ms[i], int(calls[i])) for i in range(n)}
+
+
+def count_pairs(W, H, R, binning, image):
+    """(N_eval, N_contrib) of a finished forward (see ws_debug_count_pairs)."""
+    L = _lib.load()
+    counts = torch.zeros((2,), dtype=torch.int64, device=image.device)
+    with torch.cuda.device(image.device):
+        _lib.check(L.ws_debug_count_pairs(W, H, _ptr(binning), image.data_ptr(), int(R), counts.data_ptr(), _stream()),
+                   "ws_debug_count_pairs")
+    c = counts.cpu().tolist()
+    return int(c[0]), int(c[1])

@@ -50,6 +50,17 @@ class FlashGaussianRasterizationSettings(NamedTuple):
     num_obj: int
 
 
+_GRAD_BUCKET = None
+
+
+def set_grad_bucket(bucket):
+    """Optional flat float32 buffer the next backward passes write their gradients into (layout:
+    wheat_3dgs_b200.dist.split_bucket).  A data-parallel trainer all-reduces its first
+    (14+3M)*P floats as one collective; None restores per-call allocation."""
+    global _GRAD_BUCKET
+    _GRAD_BUCKET = bucket
+
+
 def _snapshot(args, path):
     """debug=True behaviour of the reference: CPU copy of the inputs dumped when the call throws
     (DGR __init__.py:83-90,135-142)."""
@@ -116,7 +127,10 @@ class _Rasterize(torch.autograd.Function):
                 rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy, grad_color, grad_depth, grad_alpha, sh,
                 rs.sh_degree, rs.campos, geom, ctx.num_rendered, binning, image, alpha, rs.debug)
         if not ctx.flash:
-            g = _guarded(ops.rasterize_gaussians_backward, tail, rs.debug, "snapshot_bw.dump", "backward")
+            fn = ops.rasterize_gaussians_backward
+            if _GRAD_BUCKET is not None:
+                fn = lambda *a: ops.rasterize_gaussians_backward(*a, _bucket=_GRAD_BUCKET)  # noqa: E731
+            g = _guarded(fn, tail, rs.debug, "snapshot_bw.dump", "backward")
         else:
             used, gt_mask, unique_label = saved[11:14]
             g = _guarded(ops.flash_rasterize_gaussians_backward, (gt_mask, unique_label) + tail, rs.debug,
