@@ -1,0 +1,92 @@
+"""Seeded inputs of the golden cases (shared by make_golden.py and the tests).  numpy only."""
+import hashlib
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+from wheat_3dgs_b200 import scene  # noqa: E402
+
+BG = np.array([0.1, 0.2, 0.3], np.float32)
+
+# name: (P, W, H, camera index, active SH degree, kind)
+DGR_CASES = {
+    "dgr_sh3": (4000, 200, 150, 17, 3, "sh"),
+    "dgr_deg1": (3000, 97, 61, 5, 1, "sh"),          # M = 16 coefficients stored, degree 1 active
+    "dgr_precomp": (2500, 128, 96, 30, 0, "precomp"),  # colors_precomp + cov3D_precomp
+}
+FSR_CASES = {
+    # name: (P, W, H, camera index, num_obj, use unique_label)
+    "fsr_multi": (4000, 200, 150, 17, 12, False),
+    "fsr_binary_ul": (4000, 200, 150, 17, 1, True),
+}
+KNN_CASES = {"knn_5000": 5000, "knn_7": 7}
+
+
+def cov3d_from_scale_rot(scales, rots):
+    """float32 numpy version of scene/gaussian_model.py:27-31 (build_covariance_from_scaling_rotation)."""
+    r, x, y, z = [rots[:, i].astype(np.float64) for i in range(4)]
+    R = np.stack([1 - 2 * (y * y + z * z), 2 * (x * y - r * z), 2 * (x * z + r * y),
+                  2 * (x * y + r * z), 1 - 2 * (x * x + z * z), 2 * (y * z - r * x),
+                  2 * (x * z - r * y), 2 * (y * z + r * x), 1 - 2 * (x * x + y * y)], axis=1).reshape(-1, 3, 3)
+    L = R * scales.astype(np.float64)[:, None, :]
+    S = L @ L.transpose(0, 2, 1)
+    return np.ascontiguousarray(np.stack([S[:, 0, 0], S[:, 0, 1], S[:, 0, 2], S[:, 1, 1], S[:, 1, 2], S[:, 2, 2]],
+                                         axis=1), dtype=np.float32)
+
+
+def dgr_inputs(name):
+    P, W, H, ci, deg, kind = DGR_CASES[name]
+    sc = scene.synthetic_scene(P, seed=0, scale_median=0.004)
+    cam = scene.overhead_cameras(W, H)[ci]
+    lg = scene.loss_gradients((3, H, W), seed=2)
+    if kind == "precomp":
+        rng = np.random.default_rng(7)
+        g = {"means3D": sc["means3D"], "opacities": sc["opacities"],
+             "colors_precomp": rng.uniform(0, 1, size=(P, 3)).astype(np.float32),
+             "cov3D_precomp": cov3d_from_scale_rot(sc["scales"], sc["rotations"]), "head_id": sc["head_id"]}
+    else:
+        g = sc
+    return g, cam, lg, deg
+
+
+def fsr_inputs(name):
+    P, W, H, ci, num_obj, use_ul = FSR_CASES[name]
+    sc = scene.synthetic_scene(P, seed=0, scale_median=0.004)
+    cam = scene.overhead_cameras(W, H)[ci]
+    mask = scene.head_masks(sc, cam, n_labels=num_obj)
+    if num_obj == 1:
+        mask = (mask > 0).astype(np.float32)
+    ul = None
+    if use_ul:
+        ul = np.where(sc["head_id"] == 0, 1, np.where(sc["head_id"] % 3 == 0, -1, 0)).astype(np.int32)
+    return sc, cam, mask, ul, num_obj
+
+
+def knn_inputs(name):
+    P = KNN_CASES[name]
+    rng = np.random.default_rng(P)
+    return (rng.normal(size=(P, 3)) * np.array([1.0, 0.5, 0.2]) + np.array([0.3, -0.2, 1.0])).astype(np.float32)
+
+
+def votes_inputs():
+    """Vote matrix for the multi_instance_opt golden: sparse non-negative votes with exact ties."""
+    rng = np.random.default_rng(11)
+    rows, P = 9, 6000
+    a = rng.gamma(0.5, 2.0, size=(rows, P)).astype(np.float32)
+    a[rng.uniform(size=a.shape) < 0.6] = 0.0
+    a[:, :50] = 0.0                     # never seen
+    a[3, 50:100] = a[[0, 1, 2, 4, 5, 6, 7, 8], 50:100].sum(axis=0)  # near-ties
+    a[1:, 100:150] = 0.0                # only row 0 voted
+    return a
+
+
+def input_hash(arrays):
+    h = hashlib.sha256()
+    for a in arrays:
+        h.update(np.ascontiguousarray(a).tobytes())
+    return h.hexdigest()

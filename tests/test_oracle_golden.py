@@ -1,0 +1,111 @@
+"""CPU: the oracle (oracle/splat_oracle.c) against the golden outputs of the unmodified reference
+CUDA rasterizers (tests/golden/*.npz, made on a B200 by tests/golden/make_golden.py) and against
+the reference's own Python multi_instance_opt (tests/golden/labels.npz).  This is what pins the
+oracle; the GPU tests then compare libwheatsplat with the oracle AND with the same goldens."""
+import os
+
+import numpy as np
+import pytest
+
+import cases
+import oracle
+from util import GRAD_NAMES, assert_bits, assert_exact, assert_grad, assert_image
+
+
+def _load(golden_dir, name):
+    return np.load(os.path.join(golden_dir, name + ".npz"))
+
+
+def _check_inputs(g, arrays):
+    assert str(g["input_sha256"]) == cases.input_hash(arrays), "golden inputs regenerate differently on this machine"
+
+
+@pytest.mark.parametrize("name", sorted(cases.DGR_CASES))
+def test_forward_and_backward_match_reference(golden_dir, name):
+    gold = _load(golden_dir, name)
+    g, cam, lg, deg = cases.dgr_inputs(name)
+    _check_inputs(gold, [g[k] for k in sorted(g) if isinstance(g[k], np.ndarray)]
+                  + [cam["viewmatrix"], cam["projmatrix"], cam["campos"]])
+    of = oracle.forward(g, cam, cases.BG, sh_degree=deg)
+    assert of["num_rendered"] == int(gold["num_rendered"])
+    assert_exact("radii", of["radii"], gold["radii"])
+    vis = gold["radii"] > 0
+    assert_bits("depths", of["depths"][vis], gold["depths"][vis])
+    assert_bits("means2D", of["means2D"][vis], gold["means2D"].reshape(-1, 2)[vis])
+    assert_bits("conic_opacity", of["conic_opacity"][vis], gold["conic_opacity"].reshape(-1, 4)[vis])
+    assert_exact("tiles_touched", of["tiles_touched"], gold["tiles_touched"])
+    assert_exact("point_list_keys", of["point_list_keys"], gold["point_list_keys"])
+    assert_exact("point_list", of["point_list"], gold["point_list"])
+    assert_exact("ranges", of["ranges"].reshape(-1), gold["ranges"])
+    assert_exact("n_contrib", of["n_contrib"].reshape(-1), gold["n_contrib"])
+    assert_image("rgb", of["rgb"][vis], gold["rgb"].reshape(-1, 3)[vis], 1e-5)
+    assert_image("color", of["out_color"], gold["color"])
+    assert_image("depth", of["out_depth"], gold["depth"])
+    assert_image("alpha", of["out_alpha"], gold["alpha"])
+    ob = oracle.backward(g, cam, cases.BG, of, lg["dL_dcolor"], lg["dL_ddepth"], lg["dL_dalpha"], sh_degree=deg)
+    for k in GRAD_NAMES:
+        ref = gold["g_" + k]
+        assert_grad(k, ob[k].reshape(ref.shape) if ref.size else ref, ref, spread=float(gold["spread_" + k]))
+
+
+@pytest.mark.parametrize("name", sorted(cases.FSR_CASES))
+def test_flashsplat_votes_match_reference(golden_dir, name):
+    gold = _load(golden_dir, name)
+    sc, cam, mask, ul, num_obj = cases.fsr_inputs(name)
+    _check_inputs(gold, [sc["means3D"], sc["shs"], mask, cam["projmatrix"]])
+    of = oracle.forward(sc, cam, np.zeros(3, np.float32), sh_degree=3, gt_mask=mask, unique_label=ul, num_obj=num_obj)
+    assert_exact("radii", of["radii"], gold["radii"])
+    assert_exact("contrib_num", of["contrib_num"], gold["contrib_num"])
+    assert_bits("image_xys", of["image_xys"], gold["image_xys"])
+    assert_bits("gs_depth", of["gs_depth"], gold["gs_depth"])
+    assert_image("color", of["out_color"], gold["color"])
+    assert_image("alpha", of["out_alpha"], gold["alpha"])
+    ru = gold["used_count"]
+    assert_grad("used_count", of["used_count"], ru, spread=float(gold["spread_used_count"]), rtol=1e-4)
+    # final label assignment: identical wherever the reference's own vote margin is above its noise
+    lab_o, lab_r = oracle.multi_instance_opt(of["used_count"]), oracle.multi_instance_opt(ru)
+    rest = ru.sum(axis=0, keepdims=True) - ru
+    safe = (np.abs(ru - rest) > 1e-4 * (1.0 + np.abs(ru) + np.abs(rest))) | ((ru == 0) & (rest == 0))
+    assert_exact("labels", lab_o[safe], lab_r[safe])
+    assert safe.mean() > 0.99
+
+
+def test_multi_instance_opt_matches_reference_python(golden_dir):
+    gold = _load(golden_dir, "labels")
+    a = cases.votes_inputs()
+    _check_inputs(gold, [a])
+    for key in gold.files:
+        if key.startswith("labels_g"):
+            assert_exact(key, oracle.multi_instance_opt(a, float(key[len("labels_g"):])), gold[key])
+
+
+@pytest.mark.parametrize("name", sorted(cases.KNN_CASES))
+def test_knn_matches_reference(golden_dir, name):
+    gold = _load(golden_dir, name)
+    pts = cases.knn_inputs(name)
+    _check_inputs(gold, [pts])
+    assert_bits("distCUDA2", oracle.knn_dist2(pts), gold["dist2"])
+
+
+def test_sort_is_stable_and_matches_numpy():
+    rng = np.random.default_rng(0)
+    for n, bits in ((0, 40), (1, 40), (1000, 46), (70000, 43), (5000, 8)):
+        keys = rng.integers(0, 1 << 62, size=n, dtype=np.uint64)
+        keys = (keys >> np.uint64(20)) << np.uint64(20)  # many duplicates in the low sorted bits
+        vals = np.arange(n, dtype=np.uint32)
+        ko, vo = oracle.sort_pairs(keys, vals, bits)
+        order = np.argsort(keys & np.uint64((1 << bits) - 1), kind="stable")
+        assert_exact("keys", ko, keys[order])
+        assert_exact("vals", vo, vals[order])
+
+
+def test_empty_and_fully_culled_scene():
+    g, cam, lg, deg = cases.dgr_inputs("dgr_deg1")
+    g = dict(g)
+    g["means3D"] = g["means3D"].copy()
+    g["means3D"][:, 2] += 100.0  # behind every overhead camera
+    of = oracle.forward(g, cam, cases.BG, sh_degree=deg)
+    assert of["num_rendered"] == 0 and not of["radii"].any()
+    H, W = cam["image_height"], cam["image_width"]
+    assert_image("color", of["out_color"], np.broadcast_to(cases.BG[:, None, None], (3, H, W)))
+    assert not of["out_alpha"].any()
