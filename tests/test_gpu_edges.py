@@ -182,9 +182,10 @@ def test_full_size_properties_config2():
     lg = scene.loss_gradients((3, H, W), seed=2)
     dc, dd, da = G.t(lg["dL_dcolor"]), G.t(lg["dL_ddepth"]), G.t(lg["dL_dalpha"])
     g1 = [x.clone() for x in G.backward(gd, cd, bg, 3, fw, dc, dd, da)]
+    g1b = [x.clone() for x in G.backward(gd, cd, bg, 3, fw, dc, dd, da)]  # own run-to-run spread (float atomics)
     g2 = G.backward(gd, cd, bg, 3, fw, 2 * dc, 2 * dd, 2 * da)
-    for k, x1, x2 in zip(GRAD_NAMES, g1, g2):
-        assert_grad(k + " linearity", G.n(x2), 2.0 * G.n(x1), rtol=1e-4)
+    for k, x1, x1b, x2 in zip(GRAD_NAMES, g1, g1b, g2):
+        assert_grad(k + " linearity", G.n(x2), 2.0 * G.n(x1), spread=2.0 * float((x1 - x1b).abs().max()))
     inv = G.n(radii) == 0
     for k, x1 in zip(GRAD_NAMES, g1):
         assert float(x1.view(P, -1)[torch.from_numpy(inv).cuda()].abs().max()) == 0.0, k + ": culled Gaussians must get zero"
