@@ -3,7 +3,11 @@
 // backward :20-139 and cov3D backward :278-341).
 //
 // Input: the 48-byte accumulator row acc[g][12] the blend backward summed into
-//   {dL_dcolor rgb, dL_ddepth | dL_dmean2D xy, dL_dconic x y | dL_dconic w, dL_dopacity, -, -}.
+//   {dL_dcolor rgb, dL_ddepth | Sgx, Sgy, Sgxx, Sgxy | Sgyy, Sg, -, -}
+// where g = G * dL_dalpha of a (pixel, Gaussian) pair, gx = g*dx, gxx = g*dx*dx, ... summed over the
+// pixels.  With k = -0.5 * opacity:  dL_dconic = k * (Sgxx, Sgxy, Sgyy),  dL_dopacity = Sg,
+// dL_dmean2D = k * (W * (A*Sgx + B*Sgy), H * (C*Sgy + B*Sgx))  (DGR backward.cu:583-598 with the
+// per-Gaussian constants factored out of the pixel sums).
 // Output: the eight gradient tensors of rasterize_gaussians_backward; EVERY element is written
 // (zeros for culled Gaussians and for SH bands above the active degree), so the caller needs no
 // zero-fill (the reference memsets ~304 MB per call at 1 M Gaussians,
@@ -33,6 +37,7 @@ struct PreBwdParams {
     const int32_t *radii;
     const uint8_t *clamped;
     const float *acc;
+    const float4 *g0, *g1;
     float *dL_dmeans2D, *dL_dcolors, *dL_dopacity, *dL_dmeans3D, *dL_dcov3D, *dL_dsh, *dL_dscales,
         *dL_drotations;
     int sh_vec4;
@@ -142,8 +147,14 @@ __global__ void __launch_bounds__(WS_PRE_THREADS) preprocess_bwd(const PreBwdPar
             const float4 *ap = reinterpret_cast<const float4 *>(p.acc + (size_t)idx * 12);
             const float4 a0 = ap[0], a1 = ap[1], a2 = ap[2];
             a[0] = a0.x; a[1] = a0.y; a[2] = a0.z; a[3] = a0.w;
-            a[4] = a1.x; a[5] = a1.y; a[6] = a1.z; a[7] = a1.w;
-            a[8] = a2.x; a[9] = a2.y; a[10] = 0.f; a[11] = 0.f;
+            {
+                const float4 ga = p.g0[idx], gb = p.g1[idx]; // {x, y, A, B}, {C, opacity, depth, tau}
+                const float k = -0.5f * gb.y;
+                a[4] = k * (float)p.W * (ga.z * a1.x + ga.w * a1.y);
+                a[5] = k * (float)p.H * (gb.x * a1.y + ga.w * a1.x);
+                a[6] = k * a1.z; a[7] = k * a1.w; a[8] = k * a2.x;
+                a[9] = a2.y; a[10] = 0.f; a[11] = 0.f;
+            }
             const float mx = p.means3D[3 * (size_t)idx], my = p.means3D[3 * (size_t)idx + 1],
                         mz = p.means3D[3 * (size_t)idx + 2];
             float s[3] = {0.f, 0.f, 0.f}, q[4] = {0.f, 0.f, 0.f, 0.f}, c3[6];
@@ -362,7 +373,7 @@ int launch_preprocess_bwd(const ws_view *v, const ws_gaussians *g, const int32_t
     p.means3D = g->means3D; p.shs = g->shs; p.scales = g->scales; p.rotations = g->rotations;
     p.cov3D_precomp = g->cov3D_precomp;
     p.view = v->viewmatrix; p.proj = v->projmatrix; p.campos = v->campos;
-    p.radii = radii; p.clamped = gs.clamped; p.acc = gs.acc;
+    p.radii = radii; p.clamped = gs.clamped; p.acc = gs.acc; p.g0 = gs.g0; p.g1 = gs.g1;
     p.dL_dmeans2D = gr->dL_dmeans2D; p.dL_dcolors = gr->dL_dcolors; p.dL_dopacity = gr->dL_dopacity;
     p.dL_dmeans3D = gr->dL_dmeans3D; p.dL_dcov3D = gr->dL_dcov3D; p.dL_dsh = gr->dL_dsh;
     p.dL_dscales = gr->dL_dscales; p.dL_drotations = gr->dL_drotations;
