@@ -50,6 +50,136 @@ __global__ void __launch_bounds__(256) render_bwd(const RenderBwdParams p)
     __shared__ __align__(128) float4 s_q2[2][RB_BATCH];
     __shared__ __align__(8) uint64_t s_full[2];
     __shared__ uint32_t s_wmax[8];
+
+    const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+    const uint32_t tile = blockIdx.y * gridDim.x + blockIdx.x;
+    const int wx0 = blockIdx.x * WS_BLOCK_X + (w & 1) * 8;
+    const int wy0 = blockIdx.y * WS_BLOCK_Y + (w >> 1) * 4;
+    const int px = wx0 + (lane & 7), py = wy0 + (lane >> 3);
+    const bool inside = px < p.W && py < p.H;
+    const uint32_t pix_id = (uint32_t)p.W * py + px;
+    const float pixfx = (float)px, pixfy = (float)py;
+    const float fx0 = (float)wx0, fy0 = (float)wy0;
+    const size_t HW = (size_t)p.H * p.W;
+
+    const uint2 range = p.ranges[tile];
+    const uint32_t last = inside ? p.n_contrib[pix_id] : 0u; // 1-based position of last blended record
+    const uint32_t wmax = __reduce_max_sync(0xffffffffu, last);
+    if (lane == 0) s_wmax[w] = wmax;
+    if (tid == 0) {
+        mbar_init(&s_full[0], 1);
+        mbar_init(&s_full[1], 1);
+        mbar_fence_init();
+    }
+    __syncthreads();
+    uint32_t bmax = 0;
+#pragma unroll
+    for (int k = 0; k < 8; k++) bmax = max(bmax, s_wmax[k]);
+    const int n = (int)min(bmax, range.y - range.x); // records [0, n) of the tile matter
+    const int nb = (n + RB_BATCH - 1) / RB_BATCH;
+
+    auto issue = [&](int b, int s) {
+        const int cnt = min(RB_BATCH, n - b * RB_BATCH);
+        const uint32_t bytes = (uint32_t)cnt * 16u;
+        const size_t off = (size_t)range.x + (size_t)b * RB_BATCH;
+        mbar_expect_tx(&s_full[s], 3u * bytes);
+        tma_load_1d(&s_q0[s][0], p.q0 + off, bytes, &s_full[s]);
+        tma_load_1d(&s_q1[s][0], p.q1 + off, bytes, &s_full[s]);
+        tma_load_1d(&s_q2[s][0], p.q2 + off, bytes, &s_full[s]);
+    };
+
+    // per-pixel state, DGR backward.cu:461-496
+    const float T_final = inside ? (1.0f - p.out_alpha[pix_id]) : 0.0f;
+    float T = T_final;
+    float dLr = 0.f, dLg = 0.f, dLb = 0.f, dLd = 0.f, dLa = 0.f;
+    if (inside) {
+        dLr = p.dL_dcolor[pix_id];
+        dLg = p.dL_dcolor[HW + pix_id];
+        dLb = p.dL_dcolor[2 * HW + pix_id];
+        dLd = p.dL_ddepth[pix_id];
+        dLa = p.dL_dalpha[pix_id];
+    }
+    float bgdot = 0.0f;
+    bgdot += __ldg(p.bg + 0) * dLr;
+    bgdot += __ldg(p.bg + 1) * dLg;
+    bgdot += __ldg(p.bg + 2) * dLb;
+    const float nTf_bg = -T_final * bgdot; // background term of backward.cu:577-580, times 1/(1-alpha)
+    int obj_id = 0;
+    if (FLASH) {
+        if (inside && p.gt_mask) obj_id = __float2int_rz(p.gt_mask[pix_id]);
+    }
+    // running "what lies behind" sums, backward.cu:538-575: x <- last_alpha*last_x + (1-last_alpha)*x
+    float last_alpha = 0.f, lc0 = 0.f, lc1 = 0.f, lc2 = 0.f, last_depth = 0.f;
+    float ac0 = 0.f, ac1 = 0.f, ac2 = 0.f, acd = 0.f, aca = 0.f;
+
+    if (nb > 0 && tid == 0) issue(nb - 1, 0);
+    for (int it = 0; it < nb; it++) {
+        const int b = nb - 1 - it;
+        const int s = it & 1;
+        const int cnt = min(RB_BATCH, n - b * RB_BATCH);
+        if (it + 1 < nb && tid == 0) issue(b - 1, (it + 1) & 1);
+        mbar_wait(&s_full[s], (uint32_t)((it >> 1) & 1));
+
+        for (int c0 = ((cnt - 1) >> 5) << 5; c0 >= 0; c0 -= 32) {
+            const int r = c0 + lane;
+            bool hit = false;
+            if (r < cnt && (uint32_t)(b * RB_BATCH + r) < wmax)
+                hit = rect_hit(s_q0[s][r], s_q1[s][r], fx0, fy0, 7.0f, 3.0f);
+            uint32_t m = __ballot_sync(0xffffffffu, hit);
+            while (m) {
+                const int j = 31 - __clz(m);
+                m &= ~(1u << j);
+                const int rr = c0 + j;
+                const uint32_t pos0 = (uint32_t)(b * RB_BATCH + rr);
+                const float4 a = s_q0[s][rr];
+                const float4 q = s_q1[s][rr];
+                const float4 c = s_q2[s][rr];
+                const uint32_t gid = __float_as_uint(c.w);
+                float4 va = make_float4(0.f, 0.f, 0.f, 0.f), vb = make_float4(0.f, 0.f, 0.f, 0.f);
+                float2 vc = make_float2(0.f, 0.f);
+                bool act = inside && pos0 < last; // backward.cu:516-518
+                if (FLASH) {
+                    if (p.unique_label != nullptr) {
+                        const int uid = __ldg(p.unique_label + gid);
+                        if (uid >= 0 && obj_id != uid) act = false;
+                    }
+                }
+                bool contributed = false;
+                if (act) {
+                    const float dx = __fadd_rn(a.x, -pixfx), dy = __fadd_rn(a.y, -pixfy);
+                    const float t_zz = __fmul_rn(dy, __fmul_rn(dy, q.x));
+                    const float t_xx = __fmul_rn(dx, a.z);
+                    const float t_xy = __fmul_rn(dy, __fmul_rn(dx, a.w));
+                    const float power = __fmaf_rn(__fmaf_rn(dx, t_xx, t_zz), -0.5f, -t_xy);
+                    if (!(power > 0.0f)) {
+                        const float G = expf(power);
+                        const float alpha = fminf(0.99f, __fmul_rn(q.y, G));
+                        if (!(alpha < 1.0f / 255.0f)) {
+                            contributed = true;
+                            const float inv = rcp_approx(1.0f - alpha);
+                            T = T * inv; // backward.cu:534
+                            const float wgt = alpha * T;
+                            ac0 += last_alpha * (lc0 - ac0); lc0 = c.x;
+                            ac1 += last_alpha * (lc1 - ac1); lc1 = c.y;
+                            ac2 += last_alpha * (lc2 - ac2); lc2 = c.z;
+                            acd += last_alpha * (last_depth - acd); last_depth = q.z;
+                            aca += last_alpha * (1.0f - aca);
+                            last_alpha = alpha;
+                            float dL_dopa = (c.x - ac0) * dLr;
+                            dL_dopa += (c.y - ac1) * dLg;
+                            dL_dopa += (c.z - ac2) * dLb;
+                            dL_dopa += (q.z - acd) * dLd;
+                            dL_dopa += (1.0f - aca) * dLa;
+                            dL_dopa = dL_dopa * T + nTf_bg * inv;
+                            va = make_float4(wgt * dLr, wgt * dLg, wgt * dLb, wgt * dLd);
+                            const float g = G * dL_dopa;
+                            const float gx = g * dx, gy = g * dy;
+                            vb = make_float4(gx, gy, gx * dx, gx * dy);
+                            vc = make_float2(gy * dy, g);
+                        }
+                    }
+                }
+                if (__ballot_sync(0xffffffffu, contributed) == 0) continue;
                 {
                     // transposing butterfly over 8 slots (lane l ends with slot l>>2 summed over the warp)
                     float v[8] = {va.x, va.y, va.z, va.w, vb.x, vb.y, vb.z, vb.w};
