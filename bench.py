@@ -134,11 +134,13 @@ def stage_model(P, V, R, T, HW, M, npass, n_eval, n_contrib):
     """Algorithmic HBM bytes / flops per view of every stage (DESIGN.md section 4 derives them)."""
     c = 12 * M  # SH bytes per Gaussian
     by = {
-        "preprocess": P * (44 + 8) + V * (c + 49),
+        # depth-first binning (default): preprocess also writes the (depth bits, id) pair; "sort" =
+        # the depth sort of P 8-byte pairs (4 passes) + the tile sort of R 8-byte pairs (npass passes)
+        "preprocess": P * (44 + 8 + 8) + V * (c + 49),
         "scan": 8 * ((P + 255) // 256),
-        "emit_keys": 8 * P + 36 * V + 12 * R,
-        "sort": 8 * R + npass * 24 * R,
-        "ranges_pack": 12 * R + 48 * R + 8 * T,
+        "emit_keys": 12 * P + 8 * ((P + 255) // 256) + 24 * V + 8 * R,
+        "sort": (4 * P + 4 * 16 * P) + (4 * R + npass * 16 * R),
+        "ranges_pack": 8 * R + 48 * R + 8 * T,
         "render_fwd": 48 * R + 24 * HW,
         "render_bwd": 48 * R + 32 * HW + 40 * V,
         "preprocess_bwd": P * (4 + 48) + V * (44 + c) + P * (c + 92),
@@ -454,7 +456,7 @@ def main():
     peaks = load_peaks()
     st = r["stats"]
     T = ((W + 15) // 16) * ((H + 15) // 16)
-    bits = 32 + max(1, int(np.ceil(np.log2(T + 1))))
+    bits = max(1, int(np.ceil(np.log2(T + 1))))  # tile-id bits sorted per instance (depth-first binning)
     by, fl = stage_model(P, st["V"], st["R"], T, W * H, r["M"], (bits + 7) // 8, st["n_eval"], st["n_contrib"])
     stages = {}
     for name, (ms, calls) in r["prof"].items():

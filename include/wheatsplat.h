@@ -160,6 +160,19 @@ size_t ws_sort_bytes(int64_t n);
 int ws_sort_pairs_u64(int64_t n, uint64_t *keys_in, uint64_t *keys_out, uint32_t *vals_in,
                       uint32_t *vals_out, int32_t end_bit, void *scratch, size_t scratch_bytes,
                       ws_stream_t stream);
+/* Same sort on (u32 key, u32 value) pairs: the form depth-first binning uses (Gaussians by depth
+ * bits, then instances by tile id). */
+int ws_sort_pairs_u32(int64_t n, uint32_t *keys_in, uint32_t *keys_out, uint32_t *vals_in,
+                      uint32_t *vals_out, int32_t end_bit, void *scratch, size_t scratch_bytes,
+                      ws_stream_t stream);
+
+/* How the instance list is ordered.  0 (default): depth-first binning -- the P Gaussians are sorted
+ * by depth bits once, instances are emitted in that order with their tile id as the only key and
+ * stably sorted on it.  1: the reference's scheme (duplicateWithKeys' 64-bit tile|depth keys, one
+ * sort over all instances, rasterizer_impl.cu:70-111,304-309).  -1: take it from the environment
+ * (WS_BINNING=keys64).  Both produce the same point_list, ranges and images; a forward, its
+ * backward and its ws_debug_fetch calls must run under the same mode. */
+int ws_set_binning_mode(int32_t mode);
 
 /* Parity/debug access to the internal arrays of a finished forward (device -> device copy
  * into caller memory).  name is one of: "depths" f32[P], "means2D" f32[P,2],

@@ -52,6 +52,7 @@ def test_invalid_arguments_are_rejected_without_touching_the_gpu():
     assert L.ws_mark_visible(0, None, None, None, None, None) == 0
     assert L.ws_knn_dist2(0, None, None, None, 0, None) == 0
     assert L.ws_sort_pairs_u64(-1, None, None, None, None, 40, None, 0, None) == -1
+    assert L.ws_sort_pairs_u32(-1, None, None, None, None, 14, None, 0, None) == -1
     assert L.ws_multi_instance_opt(0, 0, None, 0.0, None, None) == 0
     assert L.ws_debug_fetch(b"nope", 1, 16, 16, 0, None, None, None, None, 0, None) == -1
 

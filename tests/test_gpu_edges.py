@@ -34,6 +34,25 @@ def test_radix_sort_bit_exact_and_stable(n, bits):
     assert_exact("vals", G.n(vo).view(np.uint32), rv)
 
 
+@pytest.mark.parametrize("n,bits", [(0, 14), (1, 32), (31, 14), (3072, 32), (3073, 15), (100000, 14), (777, 1),
+                                    (1 << 20, 32), (5000001, 14), (12345, 6)])
+def test_radix_sort_u32_bit_exact_and_stable(n, bits):
+    # the form depth-first binning uses: Gaussians by 32 depth bits, instances by tile id
+    gen = torch.Generator().manual_seed(7 * n + bits)
+    keys = torch.randint(0, 1 << 31, (n,), generator=gen, dtype=torch.int64)
+    if bits < 32:
+        low = (keys & ((1 << bits) - 1)) >> (bits // 3) << (bits // 3)
+        keys = low | (keys & ~((1 << bits) - 1))
+    keys = keys.to(torch.int32)
+    vals = torch.arange(n, dtype=torch.int32)
+    ko, vo = ops.sort_pairs(keys.cuda(), vals.cuda(), bits)
+    torch.cuda.synchronize()
+    k = keys.numpy().view(np.uint32)
+    order = np.argsort(k & np.uint32((1 << bits) - 1 if bits < 32 else 0xffffffff), kind="stable")
+    assert_exact("keys", G.n(ko).view(np.uint32), k[order])
+    assert_exact("vals", G.n(vo).view(np.uint32), vals.numpy().view(np.uint32)[order])
+
+
 def test_sort_all_equal_and_already_sorted():
     n = 200000
     for keys in (torch.full((n,), 0x1234_0000_0001, dtype=torch.int64), torch.arange(n, dtype=torch.int64) << 20,

@@ -33,8 +33,18 @@ def _run_dgr(name):
     return g, cam, lg, deg, fw, grads
 
 
+@pytest.fixture(params=["depth_first", "keys64"])
+def binning_mode(request):
+    """Both orderings of the instance list (ws_set_binning_mode) must give the reference's list."""
+    from wheat_3dgs_b200 import lib as wlib
+    L = wlib.load()
+    assert L.ws_set_binning_mode(0 if request.param == "depth_first" else 1) == 0
+    yield request.param
+    assert L.ws_set_binning_mode(-1) == 0
+
+
 @pytest.mark.parametrize("name", sorted(cases.DGR_CASES))
-def test_dgr_matches_reference_golden_and_oracle(golden_dir, name):
+def test_dgr_matches_reference_golden_and_oracle(golden_dir, name, binning_mode):
     gold = _gold(golden_dir, name)
     g, cam, lg, deg, fw, grads = _run_dgr(name)
     R, color, depth, alpha, radii = fw[:5]

@@ -44,6 +44,6 @@ torch.cuda.synchronize()
 pr = ops.prof_read()
 tot = 0.0
 for k, (ms, n) in pr.items():
-    print("%-16s %8.4f ms" % (k, ms / max(n, 1)))
-    tot += ms / max(n, 1)
+    print("%-16s %8.4f ms" % (k, ms / (2 * nv)))
+    tot += ms / (2 * nv)
 print("%-16s %8.4f ms" % ("sum", tot))

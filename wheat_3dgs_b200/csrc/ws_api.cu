@@ -1,6 +1,7 @@
 // ws_api.cu -- the C-ABI entry points declared in include/wheatsplat.h: argument checks,
 // scratch carving and stage sequencing.  No device memory is allocated here.
 #include <stdarg.h>
+#include <stdlib.h>
 #include <string.h>
 #include <mutex>
 #include <vector>
@@ -9,6 +10,20 @@
 namespace ws {
 
 static thread_local char g_err[512] = "";
+
+// WS_BINNING=keys64 selects the reference's own scheme (64-bit tile|depth keys, one sort over all
+// instances); the default is depth-first binning (ws_preprocess.cu).  Both give the same list.
+static int g_binning = -1; // -1: from the environment; 0: depth-first; 1: keys64
+static bool binning_keys64()
+{
+    if (g_binning >= 0) return g_binning == 1;
+    static const bool v = [] {
+        const char *e = getenv("WS_BINNING");
+        return e && !strcmp(e, "keys64");
+    }();
+    return v;
+}
+
 long long g_launch_count = 0;
 
 void set_error(const char *fmt, ...)
@@ -52,6 +67,16 @@ struct ProfScope {
         g_prof_recs.push_back({stage, a, b});
     }
 };
+
+static cudaEvent_t total_event()
+{
+    static thread_local cudaEvent_t ev[16] = {};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    dev &= 15;
+    if (!ev[dev]) cudaEventCreateWithFlags(&ev[dev], cudaEventDisableTiming);
+    return ev[dev];
+}
 
 // DGR rasterizer_impl.cu:35-50
 static uint32_t get_higher_msb(uint32_t n)
@@ -110,6 +135,12 @@ extern "C" int ws_abi_version(void) { return WS_ABI_VERSION; }
 extern "C" const char *ws_last_error(void) { return ws::g_err; }
 extern "C" int64_t ws_launch_count(void) { return ws::g_launch_count; }
 
+extern "C" int ws_set_binning_mode(int32_t mode)
+{
+    if (mode < -1 || mode > 1) { set_error("ws_set_binning_mode: mode must be -1, 0 or 1"); return WS_E_INVALID; }
+    ws::g_binning = mode;
+    return WS_OK;
+}
 extern "C" void ws_prof_enable(int32_t on) { ws::g_prof = on != 0; }
 extern "C" const char *ws_prof_stage_name(int32_t stage)
 {
@@ -173,7 +204,17 @@ extern "C" int64_t ws_forward_prepare(const ws_view *view, const ws_gaussians *g
     if (rc != WS_OK) return rc;
     uint32_t total = 0;
     WS_CUDA_CHECK(cudaMemcpyAsync(&total, gs.total, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
-    WS_CUDA_CHECK(cudaStreamSynchronize(st));
+    if (!binning_keys64()) {
+        // the depth sort needs nothing from the host: it runs while the host waits for `total`
+        // and sizes the binning scratch (the reference idles the GPU there, rasterizer_impl.cu:282)
+        cudaEvent_t ev = total_event();
+        WS_CUDA_CHECK(cudaEventRecord(ev, st));
+        { ProfScope ps(3, st); rc = launch_depth_sort(g->P, gs, st, view->debug != 0); }
+        if (rc != WS_OK) return rc;
+        WS_CUDA_CHECK(cudaEventSynchronize(ev));
+    } else {
+        WS_CUDA_CHECK(cudaStreamSynchronize(st));
+    }
     return (int64_t)total;
 }
 
@@ -207,15 +248,21 @@ extern "C" int ws_forward_render(const ws_view *view, const ws_gaussians *g, con
     ImageState is = ImageState::from((char *)image, (size_t)T, (size_t)W * H);
     BinningState bs = BinningState::from((char *)binning, R);
     uint64_t *keys = nullptr;
-    uint32_t *vals = nullptr;
-    if (R > 0) {
+    uint32_t *tkeys = nullptr, *vals = nullptr;
+    if (R > 0 && binning_keys64()) {
         { ProfScope ps(2, st); rc = launch_emit_keys(g->P, W, H, radii, gs, bs.keys_a, bs.vals_a, st, debug); }
         if (rc != WS_OK) return rc;
         const int end_bit = 32 + (int)get_higher_msb((uint32_t)T); // rasterizer_impl.cu:301-309
         { ProfScope ps(3, st); rc = launch_sort_pairs(R, bs.keys_a, bs.keys_b, bs.vals_a, bs.vals_b, end_bit, bs.sort, st, debug, &keys, &vals); }
         if (rc != WS_OK) return rc;
+    } else if (R > 0) {
+        { ProfScope ps(2, st); rc = launch_emit_tiles_ordered(g->P, W, H, radii, gs, bs.tkeys_a, bs.vals_a, st, debug); }
+        if (rc != WS_OK) return rc;
+        const int end_bit = (int)get_higher_msb((uint32_t)T);
+        { ProfScope ps(3, st); rc = launch_sort_pairs32(R, bs.tkeys_a, bs.tkeys_b, bs.vals_a, bs.vals_b, end_bit, bs.sort, st, debug, &tkeys, &vals); }
+        if (rc != WS_OK) return rc;
     }
-    { ProfScope ps(4, st); rc = launch_ranges_pack(R, T, keys, vals, gs, bs, is, st, debug); }
+    { ProfScope ps(4, st); rc = launch_ranges_pack(R, T, keys, tkeys, vals, gs, bs, is, st, debug); }
     if (rc != WS_OK) return rc;
     { ProfScope ps(5, st); rc = launch_render_fwd(view, g->P, gs, bs, is, out_color, out_depth, out_alpha, fl, st); }
     return rc;
@@ -267,6 +314,12 @@ __global__ void unpack_geom(int P, int what, const float4 *__restrict__ g0, cons
 } // namespace ws
 
 namespace ws {
+__global__ void rebuild_keys64(size_t R, const uint32_t *__restrict__ tkeys, const uint32_t *__restrict__ vals,
+                               const float4 *__restrict__ g1, uint64_t *__restrict__ keys)
+{
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < R) keys[i] = ((uint64_t)tkeys[i] << 32) | __float_as_uint(g1[vals[i]].z);
+}
 // one thread per pixel: re-walks its tile's packed records up to the pixel's last contributor
 __global__ void __launch_bounds__(256) count_pairs(int W, int H, const uint2 *__restrict__ ranges,
                                                    const uint32_t *__restrict__ n_contrib,
@@ -347,11 +400,21 @@ extern "C" int64_t ws_debug_fetch(const char *name, int32_t P, int32_t width, in
         if (R == 0) return 0;
         BinningState bs = BinningState::from((char *)binning, R);
         // the sorted pairs end in the "a" buffers after an even number of passes, else in "b"
-        const int end_bit = 32 + (int)ws::get_higher_msb((uint32_t)T);
+        const bool k64 = ws::binning_keys64();
+        const int end_bit = (k64 ? 32 : 0) + (int)ws::get_higher_msb((uint32_t)T);
         const int npass = (end_bit + 7) / 8;
         const bool in_b = (npass & 1) != 0;
-        if (!strcmp(name, "point_list_keys")) { src = in_b ? bs.keys_b : bs.keys_a; need = 8 * R; }
-        else { src = in_b ? bs.vals_b : bs.vals_a; need = 4 * R; }
+        if (!strcmp(name, "point_list")) { src = in_b ? bs.vals_b : bs.vals_a; need = 4 * R; }
+        else if (k64) { src = in_b ? bs.keys_b : bs.keys_a; need = 8 * R; }
+        else {
+            // depth-first binning sorts tile ids only: rebuild the reference's tile|depth keys
+            need = 8 * R;
+            if (dst_bytes < need) { set_error("ws_debug_fetch: dst too small"); return WS_E_SCRATCH; }
+            ws::rebuild_keys64<<<(unsigned)((R + 255) / 256), 256, 0, st>>>(
+                R, in_b ? bs.tkeys_b : bs.tkeys_a, in_b ? bs.vals_b : bs.vals_a, gs.g1, (uint64_t *)dst);
+            WS_LAUNCH_CHECK(st, false);
+            return (int64_t)need;
+        }
     } else {
         set_error("ws_debug_fetch: unknown array '%s'", name);
         return WS_E_INVALID;

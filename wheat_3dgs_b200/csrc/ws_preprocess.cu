@@ -38,6 +38,7 @@ struct PreParams {
     int32_t *radii;
     float4 *g0, *g1, *g2;
     uint32_t *tiles_touched, *block_sums;
+    uint32_t *dkeys, *dvals; // depth bits (culled: 0xffffffff) and Gaussian id, input of the depth sort
     uint8_t *clamped;
     float *image_xys, *gs_depth; // flashsplat extras or NULL
     int sh_vec4;                 // 1: 3M % 4 == 0 and shs 16-byte aligned -> float4 staging
@@ -180,7 +181,7 @@ __global__ void __launch_bounds__(WS_PRE_THREADS) preprocess_fwd(const PreParams
     }
     __syncthreads();
 
-    uint32_t my_tiles = 0;
+    uint32_t my_tiles = 0, my_dkey = 0xffffffffu;
     if (idx < p.P) {
         int my_rad = 0;
         const float *v = s_view, *pm = s_proj;
@@ -253,11 +254,14 @@ __global__ void __launch_bounds__(WS_PRE_THREADS) preprocess_fwd(const PreParams
                     if (p.gs_depth) p.gs_depth[idx] = pvz; // FSR forward.cu:258
                     my_rad = radius;
                     my_tiles = tiles;
+                    my_dkey = __float_as_uint(pvz);
                 }
             }
         }
         p.radii[idx] = my_rad;
         p.tiles_touched[idx] = my_tiles;
+        p.dkeys[idx] = my_dkey;
+        p.dvals[idx] = (uint32_t)idx;
     }
     // block sum of tiles_touched
     uint32_t s = my_tiles;
@@ -289,6 +293,7 @@ int launch_preprocess(const ws_view *v, const ws_gaussians *g, int32_t *radii, G
     p.view = v->viewmatrix; p.proj = v->projmatrix; p.campos = v->campos;
     p.radii = radii; p.g0 = gs.g0; p.g1 = gs.g1; p.g2 = gs.g2;
     p.tiles_touched = gs.tiles_touched; p.block_sums = gs.block_sums; p.clamped = gs.clamped;
+    p.dkeys = gs.dkeys_a; p.dvals = gs.dvals_a;
     p.image_xys = fl ? fl->image_xys : nullptr;
     p.gs_depth = fl ? fl->gs_depth : nullptr;
     const int row_f = 3 * g->M;
@@ -432,6 +437,118 @@ int launch_emit_keys(int P, int W, int H, const int32_t *radii, GeomState &gs, u
     const int nb = (P + WS_PRE_THREADS - 1) / WS_PRE_THREADS;
     emit_keys<<<nb, WS_PRE_THREADS, 0, st>>>(P, gx, gy, radii, gs.g0, gs.g1, gs.tiles_touched,
                                              gs.block_offsets, keys, vals);
+    WS_LAUNCH_CHECK(st, debug);
+    return WS_OK;
+}
+
+// ---- depth-first binning (default) ----
+// The reference sorts R = sum(tiles_touched) 64-bit tile|depth keys (6 byte-passes at 46 bits).
+// The same list comes out of two smaller sorts: (1) the P Gaussians by their 32-bit depth bits
+// (stable, so equal depths keep ascending id), (2) instances emitted in that order, stably sorted
+// by their tile id alone (14 bits at config 2: 2 passes over 8-byte pairs instead of 6 over
+// 12-byte pairs).  A stable sort by tile of a depth-ordered list is the stable sort by
+// (tile, depth) of the id-ordered list: point_list is bit-identical (tests compare it, and the
+// reconstructed tile|depth keys, with the reference's).
+int launch_depth_sort(int P, GeomState &gs, cudaStream_t st, bool debug)
+{
+    uint32_t *kf, *vf;
+    return launch_sort_pairs32((size_t)P, gs.dkeys_a, gs.dkeys_b, gs.dvals_a, gs.dvals_b, 32, gs.dsort, st, debug,
+                               &kf, &vf); // 4 passes: the result is back in the "a" buffers
+}
+const uint32_t *depth_order(const GeomState &gs) { return gs.dvals_a; }
+
+// tiles_touched summed over blocks of 256 Gaussians taken in depth order
+__global__ void __launch_bounds__(WS_PRE_THREADS) ordered_block_sums(int P, const uint32_t *__restrict__ order,
+                                                                     const uint32_t *__restrict__ tiles_touched,
+                                                                     uint32_t *__restrict__ block_sums)
+{
+    __shared__ uint32_t s_w[WS_PRE_THREADS / 32];
+    const int i = blockIdx.x * WS_PRE_THREADS + threadIdx.x;
+    uint32_t s = i < P ? tiles_touched[order[i]] : 0u;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    if ((threadIdx.x & 31) == 0) s_w[threadIdx.x >> 5] = s;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t t = 0;
+#pragma unroll
+        for (int w = 0; w < WS_PRE_THREADS / 32; w++) t += s_w[w];
+        block_sums[blockIdx.x] = t;
+    }
+}
+
+// emit_keys over the depth-ordered Gaussians: key = tile id only, value = Gaussian id
+__global__ void __launch_bounds__(WS_PRE_THREADS) emit_tiles_ordered(int P, int gx, int gy,
+                                                                     const uint32_t *__restrict__ order,
+                                                                     const int32_t *__restrict__ radii,
+                                                                     const float4 *__restrict__ g0,
+                                                                     const uint32_t *__restrict__ tiles_touched,
+                                                                     const uint32_t *__restrict__ block_offsets,
+                                                                     uint32_t *__restrict__ tkeys,
+                                                                     uint32_t *__restrict__ vals)
+{
+    __shared__ uint32_t s_w[WS_PRE_THREADS / 32];
+    const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+    const int i = blockIdx.x * WS_PRE_THREADS + tid;
+    uint32_t tt = 0, rminx = 0, rminy = 0, width = 1, gid = 0;
+    if (i < P) {
+        gid = order[i];
+        const int rad = radii[gid];
+        if (rad > 0) {
+            tt = tiles_touched[gid];
+            const float4 a = g0[gid];
+            uint2 rmin, rmax;
+            get_rect(a.x, a.y, rad, gx, gy, rmin, rmax);
+            rminx = rmin.x; rminy = rmin.y; width = rmax.x - rmin.x;
+        }
+    }
+    uint32_t inc = tt;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        uint32_t n = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += n;
+    }
+    const uint32_t warp_total = __shfl_sync(0xffffffffu, inc, 31);
+    if (lane == 31) s_w[w] = inc;
+    __syncthreads();
+    uint32_t warp_base = block_offsets[blockIdx.x];
+    for (int k = 0; k < w; k++) warp_base += s_w[k];
+    const uint32_t excl = inc - tt;
+    for (uint32_t k0 = 0; k0 < warp_total; k0 += 32) {
+        const uint32_t k = k0 + lane;
+        int j = 0; // number of lanes whose inclusive sum <= k  == owner lane
+#pragma unroll
+        for (int s = 16; s >= 1; s >>= 1) {
+            uint32_t vv = __shfl_sync(0xffffffffu, inc, min(j + s - 1, 31));
+            if (vv <= k) j += s;
+        }
+        j = min(j, 31);
+        const uint32_t o_excl = __shfl_sync(0xffffffffu, excl, j);
+        const uint32_t o_minx = __shfl_sync(0xffffffffu, rminx, j);
+        const uint32_t o_miny = __shfl_sync(0xffffffffu, rminy, j);
+        const uint32_t o_w = __shfl_sync(0xffffffffu, width, j);
+        const uint32_t o_id = __shfl_sync(0xffffffffu, gid, j);
+        if (k < warp_total) {
+            const uint32_t local = k - o_excl;
+            const uint32_t ty = local / o_w, tx = local - ty * o_w;
+            tkeys[(size_t)warp_base + k] = (o_miny + ty) * (uint32_t)gx + (o_minx + tx);
+            vals[(size_t)warp_base + k] = o_id;
+        }
+    }
+}
+
+int launch_emit_tiles_ordered(int P, int W, int H, const int32_t *radii, GeomState &gs, uint32_t *tkeys,
+                              uint32_t *vals, cudaStream_t st, bool debug)
+{
+    const int gx = (W + WS_BLOCK_X - 1) / WS_BLOCK_X, gy = (H + WS_BLOCK_Y - 1) / WS_BLOCK_Y;
+    const int nb = (P + WS_PRE_THREADS - 1) / WS_PRE_THREADS;
+    const uint32_t *order = depth_order(gs);
+    ordered_block_sums<<<nb, WS_PRE_THREADS, 0, st>>>(P, order, gs.tiles_touched, gs.block_sums);
+    WS_LAUNCH_CHECK(st, debug);
+    scan_block_sums<<<1, 1024, 0, st>>>(nb, gs.block_sums, gs.block_offsets, gs.total + 1);
+    WS_LAUNCH_CHECK(st, debug);
+    emit_tiles_ordered<<<nb, WS_PRE_THREADS, 0, st>>>(P, gx, gy, order, radii, gs.g0, gs.tiles_touched,
+                                                      gs.block_offsets, tkeys, vals);
     WS_LAUNCH_CHECK(st, debug);
     return WS_OK;
 }

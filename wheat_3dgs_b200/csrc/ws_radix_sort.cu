@@ -44,7 +44,8 @@ SortScratch SortScratch::from(char *&p, size_t n)
     return s;
 }
 
-__global__ void __launch_bounds__(256) rs_histogram(const uint64_t *__restrict__ keys, size_t n, int end_bit,
+template <typename K>
+__global__ void __launch_bounds__(256) rs_histogram(const K *__restrict__ keys, size_t n, int end_bit,
                                                     uint32_t *__restrict__ hist)
 {
     __shared__ uint32_t sh[RS_MAX_PASSES * 256];
@@ -53,7 +54,7 @@ __global__ void __launch_bounds__(256) rs_histogram(const uint64_t *__restrict__
     __syncthreads();
     const size_t stride = (size_t)gridDim.x * blockDim.x;
     for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-        const uint64_t key = keys[i];
+        const K key = keys[i];
         for (int p = 0; p < npass; p++) {
             const int bits = min(8, end_bit - 8 * p);
             const uint32_t d = (uint32_t)(key >> (8 * p)) & ((1u << bits) - 1u);
@@ -106,13 +107,14 @@ __device__ __forceinline__ void st_relaxed(uint32_t *p, uint32_t v)
     asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 
+template <typename K>
 __global__ void __launch_bounds__(RS_THREADS)
-rs_onesweep(const uint64_t *__restrict__ keys_in, uint64_t *__restrict__ keys_out,
+rs_onesweep(const K *__restrict__ keys_in, K *__restrict__ keys_out,
             const uint32_t *__restrict__ vals_in, uint32_t *__restrict__ vals_out, size_t n, int shift,
             int bits, const uint32_t *__restrict__ bins, uint32_t *__restrict__ counter,
             uint32_t *__restrict__ status)
 {
-    __shared__ uint64_t s_keys[RS_TILE];          // 24 KB
+    __shared__ K s_keys[RS_TILE];                 // 24 KB (u64) / 12 KB (u32)
     __shared__ uint32_t s_vals[RS_TILE];          // 12 KB
     __shared__ uint32_t s_whist[RS_WARPS][256];   //  8 KB
     __shared__ uint32_t s_dstart[256];
@@ -132,14 +134,14 @@ rs_onesweep(const uint64_t *__restrict__ keys_in, uint64_t *__restrict__ keys_ou
     const size_t base = (size_t)tile * RS_TILE;
     const size_t seg = base + (size_t)w * (RS_ITEMS * 32);
 
-    uint64_t key[RS_ITEMS];
+    K key[RS_ITEMS];
     uint32_t val[RS_ITEMS];
     uint32_t rank[RS_ITEMS];
 #pragma unroll
     for (int i = 0; i < RS_ITEMS; i++) {
         const size_t idx = seg + (size_t)i * 32 + lane;
         const bool valid = idx < n;
-        key[i] = valid ? keys_in[idx] : ~0ull;
+        key[i] = valid ? keys_in[idx] : (K)~(K)0;
         val[i] = valid ? vals_in[idx] : 0u;
     }
 
@@ -210,7 +212,7 @@ rs_onesweep(const uint64_t *__restrict__ keys_in, uint64_t *__restrict__ keys_ou
     for (int j = 0; j < RS_ITEMS; j++) {
         const uint32_t p = tid + j * RS_THREADS;
         if (p < ntile) {
-            const uint64_t k = s_keys[p];
+            const K k = s_keys[p];
             const uint32_t d = (uint32_t)(k >> shift) & mask;
             const size_t dst = (size_t)(s_goff[d] + p);
             keys_out[dst] = k;
@@ -219,9 +221,10 @@ rs_onesweep(const uint64_t *__restrict__ keys_in, uint64_t *__restrict__ keys_ou
     }
 }
 
-int launch_sort_pairs(size_t n, uint64_t *keys_in, uint64_t *keys_out, uint32_t *vals_in,
-                      uint32_t *vals_out, int end_bit, SortScratch &ss, cudaStream_t st, bool debug,
-                      uint64_t **keys_final, uint32_t **vals_final)
+template <typename K>
+static int sort_pairs_impl(size_t n, K *keys_in, K *keys_out, uint32_t *vals_in,
+                           uint32_t *vals_out, int end_bit, SortScratch &ss, cudaStream_t st, bool debug,
+                           K **keys_final, uint32_t **vals_final)
 {
     *keys_final = keys_in;
     *vals_final = vals_in;
@@ -230,7 +233,7 @@ int launch_sort_pairs(size_t n, uint64_t *keys_in, uint64_t *keys_out, uint32_t 
         set_error("radix sort: %zu pairs exceed the 2^30-1 limit of the look-back status words", n);
         return WS_E_UNSUPPORTED;
     }
-    if (end_bit < 1 || end_bit > 64) {
+    if (end_bit < 1 || end_bit > (int)sizeof(K) * 8) {
         set_error("radix sort: end_bit %d out of range", end_bit);
         return WS_E_INVALID;
     }
@@ -240,23 +243,39 @@ int launch_sort_pairs(size_t n, uint64_t *keys_in, uint64_t *keys_out, uint32_t 
     WS_CUDA_CHECK(cudaMemsetAsync(ss.status, 0, (size_t)npass * nt * 256 * sizeof(uint32_t), st));
     int hb = (int)((n + 256 * 16 - 1) / (256 * 16));
     if (hb > 148 * 8) hb = 148 * 8;
-    rs_histogram<<<hb, 256, 0, st>>>(keys_in, n, end_bit, ss.hist);
+    rs_histogram<K><<<hb, 256, 0, st>>>(keys_in, n, end_bit, ss.hist);
     WS_LAUNCH_CHECK(st, debug);
     rs_scan_hist<<<npass, 256, 0, st>>>(ss.hist);
     WS_LAUNCH_CHECK(st, debug);
-    uint64_t *ki = keys_in, *ko = keys_out;
+    K *ki = keys_in, *ko = keys_out;
     uint32_t *vi = vals_in, *vo = vals_out;
     for (int p = 0; p < npass; p++) {
         const int bits = end_bit - 8 * p < 8 ? end_bit - 8 * p : 8;
-        rs_onesweep<<<(unsigned)nt, RS_THREADS, 0, st>>>(ki, ko, vi, vo, n, 8 * p, bits, ss.hist + p * 256,
+        rs_onesweep<K><<<(unsigned)nt, RS_THREADS, 0, st>>>(ki, ko, vi, vo, n, 8 * p, bits, ss.hist + p * 256,
                                                          ss.counters + p, ss.status + (size_t)p * nt * 256);
         WS_LAUNCH_CHECK(st, debug);
-        uint64_t *tk = ki; ki = ko; ko = tk;
+        K *tk = ki; ki = ko; ko = tk;
         uint32_t *tv = vi; vi = vo; vo = tv;
     }
     *keys_final = ki;
     *vals_final = vi;
     return WS_OK;
+}
+
+int launch_sort_pairs(size_t n, uint64_t *keys_in, uint64_t *keys_out, uint32_t *vals_in,
+                      uint32_t *vals_out, int end_bit, SortScratch &ss, cudaStream_t st, bool debug,
+                      uint64_t **keys_final, uint32_t **vals_final)
+{
+    return sort_pairs_impl<uint64_t>(n, keys_in, keys_out, vals_in, vals_out, end_bit, ss, st, debug, keys_final,
+                                     vals_final);
+}
+
+int launch_sort_pairs32(size_t n, uint32_t *keys_in, uint32_t *keys_out, uint32_t *vals_in,
+                        uint32_t *vals_out, int end_bit, SortScratch &ss, cudaStream_t st, bool debug,
+                        uint32_t **keys_final, uint32_t **vals_final)
+{
+    return sort_pairs_impl<uint32_t>(n, keys_in, keys_out, vals_in, vals_out, end_bit, ss, st, debug, keys_final,
+                                     vals_final);
 }
 
 } // namespace ws
@@ -289,6 +308,31 @@ extern "C" int ws_sort_pairs_u64(int64_t n, uint64_t *keys_in, uint64_t *keys_ou
     if (rc != WS_OK) return rc;
     if (n > 0 && kf != keys_out) {
         WS_CUDA_CHECK(cudaMemcpyAsync(keys_out, kf, (size_t)n * 8, cudaMemcpyDeviceToDevice, st));
+        WS_CUDA_CHECK(cudaMemcpyAsync(vals_out, vf, (size_t)n * 4, cudaMemcpyDeviceToDevice, st));
+    }
+    return WS_OK;
+}
+
+extern "C" int ws_sort_pairs_u32(int64_t n, uint32_t *keys_in, uint32_t *keys_out, uint32_t *vals_in,
+                                 uint32_t *vals_out, int32_t end_bit, void *scratch, size_t scratch_bytes,
+                                 ws_stream_t stream)
+{
+    if (n < 0 || (n > 0 && (!keys_in || !keys_out || !vals_in || !vals_out || !scratch))) {
+        ws::set_error("ws_sort_pairs_u32: bad arguments");
+        return WS_E_INVALID;
+    }
+    if (scratch_bytes < ws_sort_bytes(n)) {
+        ws::set_error("ws_sort_pairs_u32: scratch too small (%zu < %zu)", scratch_bytes, ws_sort_bytes(n));
+        return WS_E_SCRATCH;
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    char *p = (char *)scratch;
+    ws::SortScratch ss = ws::SortScratch::from(p, (size_t)n);
+    uint32_t *kf, *vf;
+    int rc = ws::launch_sort_pairs32((size_t)n, keys_in, keys_out, vals_in, vals_out, end_bit, ss, st, false, &kf, &vf);
+    if (rc != WS_OK) return rc;
+    if (n > 0 && kf != keys_out) {
+        WS_CUDA_CHECK(cudaMemcpyAsync(keys_out, kf, (size_t)n * 4, cudaMemcpyDeviceToDevice, st));
         WS_CUDA_CHECK(cudaMemcpyAsync(vals_out, vf, (size_t)n * 4, cudaMemcpyDeviceToDevice, st));
     }
     return WS_OK;

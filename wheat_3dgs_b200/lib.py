@@ -15,7 +15,7 @@ WS_ABI_VERSION = 1
 SYMBOLS = [
     "ws_abi_version", "ws_last_error", "ws_geom_bytes", "ws_image_bytes", "ws_binning_bytes",
     "ws_forward_prepare", "ws_forward_render", "ws_backward", "ws_mark_visible", "ws_knn_bytes",
-    "ws_knn_dist2", "ws_multi_instance_opt", "ws_sort_bytes", "ws_sort_pairs_u64", "ws_debug_fetch",
+    "ws_knn_dist2", "ws_multi_instance_opt", "ws_sort_bytes", "ws_sort_pairs_u64", "ws_sort_pairs_u32", "ws_set_binning_mode", "ws_debug_fetch",
     "ws_launch_count", "ws_prof_enable", "ws_prof_read", "ws_prof_stage_name", "ws_debug_count_pairs",
 ]
 WS_PROF_NSTAGES = 8
@@ -98,6 +98,10 @@ def load():
     lib.ws_sort_bytes.argtypes = [i64]
     lib.ws_sort_pairs_u64.restype = C.c_int
     lib.ws_sort_pairs_u64.argtypes = [i64, vp, vp, vp, vp, i32, vp, sz, vp]
+    lib.ws_set_binning_mode.restype = C.c_int
+    lib.ws_set_binning_mode.argtypes = [i32]
+    lib.ws_sort_pairs_u32.restype = C.c_int
+    lib.ws_sort_pairs_u32.argtypes = [i64, vp, vp, vp, vp, i32, vp, sz, vp]
     lib.ws_debug_fetch.restype = i64
     lib.ws_debug_fetch.argtypes = [C.c_char_p, i32, i32, i32, i64, vp, vp, vp, vp, sz, vp]
     lib.ws_prof_enable.restype = None

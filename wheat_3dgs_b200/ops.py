@@ -268,17 +268,19 @@ def multi_instance_opt(all_contrib, gamma=0.0):
 
 
 def sort_pairs(keys, vals, end_bit):
-    """Stable radix sort of (int64-viewed-as-u64 keys, int32-viewed-as-u32 vals) on bits [0,end_bit)."""
+    """Stable radix sort of (int64-viewed-as-u64 or int32-viewed-as-u32 keys, int32-viewed-as-u32 vals)
+    on key bits [0,end_bit)."""
     L = _lib.load()
+    fn, fname = (L.ws_sort_pairs_u64, "ws_sort_pairs_u64") if keys.element_size() == 8 else \
+        (L.ws_sort_pairs_u32, "ws_sort_pairs_u32")
     n = keys.numel()
     k_in, v_in = keys.clone().contiguous(), vals.clone().contiguous()
     k_out, v_out = torch.empty_like(k_in), torch.empty_like(v_in)
     if n:
         scratch = torch.empty((L.ws_sort_bytes(n),), dtype=torch.uint8, device=keys.device)
         with torch.cuda.device(keys.device):
-            _lib.check(L.ws_sort_pairs_u64(n, k_in.data_ptr(), k_out.data_ptr(), v_in.data_ptr(), v_out.data_ptr(),
-                                           int(end_bit), scratch.data_ptr(), scratch.numel(), _stream()),
-                       "ws_sort_pairs_u64")
+            _lib.check(fn(n, k_in.data_ptr(), k_out.data_ptr(), v_in.data_ptr(), v_out.data_ptr(),
+                          int(end_bit), scratch.data_ptr(), scratch.numel(), _stream()), fname)
     return k_out, v_out
 
 
