@@ -27,6 +27,7 @@ constexpr int RS_WARPS = RS_THREADS / 32;
 constexpr int RS_ITEMS = 12;
 constexpr int RS_TILE = RS_THREADS * RS_ITEMS; // 3072 pairs per CTA
 constexpr int RS_MAX_PASSES = 8;
+constexpr int RS_LOOK = 8;
 
 constexpr uint32_t RS_FLAG_AGG = 1u << 30; // tile aggregate available
 constexpr uint32_t RS_FLAG_INC = 2u << 30; // inclusive prefix available
@@ -108,7 +109,7 @@ __device__ __forceinline__ void st_relaxed(uint32_t *p, uint32_t v)
 }
 
 template <typename K>
-__global__ void __launch_bounds__(RS_THREADS)
+__global__ void __launch_bounds__(RS_THREADS, sizeof(K) == 4 ? 4 : 3)
 rs_onesweep(const K *__restrict__ keys_in, K *__restrict__ keys_out,
             const uint32_t *__restrict__ vals_in, uint32_t *__restrict__ vals_out, size_t n, int shift,
             int bits, const uint32_t *__restrict__ bins, uint32_t *__restrict__ counter,
@@ -174,17 +175,27 @@ rs_onesweep(const K *__restrict__ keys_in, K *__restrict__ keys_out,
         st_relaxed(my_status, run | RS_FLAG_INC);
     } else {
         st_relaxed(my_status, run | RS_FLAG_AGG);
+        // Look-back, RS_LOOK predecessors per round trip (one dependent L2 round trip per
+        // predecessor serialises the pass: the tiles just before this one started at about the
+        // same time and have only their aggregate out).
         int look = (int)tile - 1;
-        while (true) {
-            const uint32_t *ps = status + (size_t)look * 256 + tid;
-            uint32_t v = ld_relaxed(ps);
-            while ((v & (RS_FLAG_AGG | RS_FLAG_INC)) == 0) {
-                __nanosleep(20);
-                v = ld_relaxed(ps);
+        bool found = false;
+        while (!found) {
+            uint32_t v[RS_LOOK];
+#pragma unroll
+            for (int k = 0; k < RS_LOOK; k++)
+                v[k] = (look - k >= 0) ? ld_relaxed(status + (size_t)(look - k) * 256 + tid) : RS_FLAG_INC;
+            int used = 0;
+#pragma unroll
+            for (int k = 0; k < RS_LOOK; k++) {
+                if (!found && used == k && (v[k] & (RS_FLAG_AGG | RS_FLAG_INC)) != 0) {
+                    excl += v[k] & RS_VAL_MASK;
+                    used = k + 1;
+                    found = (v[k] & RS_FLAG_INC) != 0;
+                }
             }
-            excl += v & RS_VAL_MASK;
-            if (v & RS_FLAG_INC) break;
-            look--;
+            look -= used;
+            if (!found && used == 0) __nanosleep(20);
         }
         st_relaxed(my_status, ((excl + run) & RS_VAL_MASK) | RS_FLAG_INC);
     }
