@@ -1,8 +1,14 @@
 // ws_render_fwd.cu -- forward alpha blending (replaces renderCUDA, DGR forward.cu:261-381, and
 // the flashsplat variant FSR forward.cu:269-418).
 //
-// One CTA per 16x16 tile, 256 threads; warp w owns the 8x4 pixel block
-// (x0 + (w&1)*8 .. +7, y0 + (w>>1)*4 .. +3), lane l the pixel (l&7, l>>3) of it.
+// One CTA per 16x16 tile, 128 threads; warp w owns the 8x8 pixel block
+// (x0 + (w&1)*8 .. +7, y0 + (w>>1)*8 .. +7) and every lane TWO pixels of it, (l&7, l>>3) and
+// (l&7, (l>>3)+4).  The two pixels share dx, so the per-pair arithmetic runs as packed f32x2
+// instructions (FADD2/FMUL2/FFMA2, sm_100: one issue slot does both pixels, scalar operands
+// broadcast for free) and the per-record overhead (bit scan, 3 LDS.128, loop control) is paid once
+// per 64 pixels.  Every packed op is the same IEEE operation, in the same order, the reference
+// build performs per pixel (its FMA contraction read from its SASS, expf2 = its expf sequence), so
+// colour, depth, alpha and n_contrib stay bit-identical to the reference.
 //
 // Staging: the tile's instance records were gathered into tile order by identify_ranges_pack,
 // so a batch of 256 records is three contiguous 4 KB runs (q0,q1,q2).  Thread 0 brings batch
@@ -11,23 +17,25 @@
 // mbarrier's phase parity.  No thread issues a per-record global load.
 //
 // Sub-tile culling: before the per-pixel loop each lane tests one record of a 32-record chunk
-// against the warp's 8x4 pixel rectangle: the exact minimum of the quadratic form
+// against the warp's 8x8 pixel rectangle: the exact minimum of the quadratic form
 // q = 1/2(A dx^2 + C dy^2) + B dx dy over the rectangle (a convex minimum lies on the two edges
 // facing the centre) is compared with tau = ln(255*opacity) plus a rounding margin.  Records
 // that cannot reach alpha >= 1/255 anywhere in the rectangle are dropped by a ballot; the warp
 // then walks only the set bits.  Dropped records would have been skipped by every pixel's own
-// test (forward.cu:337-347), so results are unchanged; the surviving pairs are evaluated with
-// exactly the reference's float operations (FMA contraction read from its SASS), in the same
-// front-to-back order, including `contributor` positions, so n_contrib is the reference's.
+// test (forward.cu:337-347), so results are unchanged, including `contributor` positions.
+//
+// A pixel that skips a record (power > 0, alpha < 1/255, finished, wrong label) takes part in the
+// packed blend with alpha = 0, which leaves its accumulators bit-for-bit unchanged.
 //
 // Early termination: a pixel stops when T would fall below 1e-4 (forward.cu:348-353); a warp
-// leaves a batch when all 32 lanes are done (warp vote); the CTA stops fetching when
-// __syncthreads_count says all 256 are done (forward.cu:305-308).
+// leaves a batch when all 64 pixels are done (warp vote); the CTA stops fetching when
+// __syncthreads_count says all 128 threads are done (forward.cu:305-308).
 #include "ws_common.cuh"
 
 namespace ws {
 
 constexpr int RF_BATCH = 256;
+constexpr int RF_THREADS = 128;
 
 struct RenderFwdParams {
     const uint2 *ranges;
@@ -45,7 +53,7 @@ struct RenderFwdParams {
 };
 
 template <bool FLASH>
-__global__ void __launch_bounds__(256) render_fwd(const RenderFwdParams p)
+__global__ void __launch_bounds__(RF_THREADS) render_fwd(const RenderFwdParams p)
 {
     __shared__ __align__(128) float4 s_q0[2][RF_BATCH];
     __shared__ __align__(128) float4 s_q1[2][RF_BATCH];
@@ -56,11 +64,12 @@ __global__ void __launch_bounds__(256) render_fwd(const RenderFwdParams p)
     const int tiles_x = gridDim.x;
     const uint32_t tile = blockIdx.y * tiles_x + blockIdx.x;
     const int wx0 = blockIdx.x * WS_BLOCK_X + (w & 1) * 8;
-    const int wy0 = blockIdx.y * WS_BLOCK_Y + (w >> 1) * 4;
-    const int px = wx0 + (lane & 7), py = wy0 + (lane >> 3);
-    const bool inside = px < p.W && py < p.H;
-    const uint32_t pix_id = (uint32_t)p.W * py + px;
-    const float pixfx = (float)px, pixfy = (float)py;
+    const int wy0 = blockIdx.y * WS_BLOCK_Y + (w >> 1) * 8;
+    const int px = wx0 + (lane & 7), py0 = wy0 + (lane >> 3), py1 = py0 + 4;
+    const bool in0 = px < p.W && py0 < p.H, in1 = px < p.W && py1 < p.H;
+    const uint32_t pix0 = (uint32_t)p.W * py0 + px, pix1 = pix0 + 4u * (uint32_t)p.W;
+    const float pixfx = (float)px;
+    const f2 npy = pk2(-(float)py0, -(float)py1);
     const float fx0 = (float)wx0, fy0 = (float)wy0;
 
     const uint2 range = p.ranges[tile];
@@ -85,15 +94,20 @@ __global__ void __launch_bounds__(256) render_fwd(const RenderFwdParams p)
         tma_load_1d(&s_q2[s][0], p.q2 + off, bytes, &s_full[s]);
     };
 
-    int obj_id = 0;
+    int obj0 = 0, obj1 = 0;
     if (FLASH) {
-        if (inside) obj_id = __float2int_rz(p.gt_mask[pix_id]);
+        if (in0) obj0 = __float2int_rz(p.gt_mask[pix0]);
+        if (in1) obj1 = __float2int_rz(p.gt_mask[pix1]);
     }
-    const bool obj_ok = FLASH ? (obj_id >= 0 && obj_id <= p.num_obj) : true;
+    const bool ok0 = FLASH ? (obj0 >= 0 && obj0 <= p.num_obj) : true;
+    const bool ok1 = FLASH ? (obj1 >= 0 && obj1 <= p.num_obj) : true;
 
-    bool done = !inside;
-    float T = 1.0f, C0 = 0.0f, C1 = 0.0f, C2 = 0.0f, weight = 0.0f, D = 0.0f;
-    uint32_t last_contributor = 0;
+    uint32_t live = (in0 ? 1u : 0u) | (in1 ? 2u : 0u); // bit i: pixel i still blending
+    // loop-carried state as scalar halves (packed only at the point of use: ptxas copies 64-bit
+    // loop-carried values through temporaries otherwise)
+    float Ta = 1.0f, Tb = 1.0f, C0a = 0.f, C0b = 0.f, C1a = 0.f, C1b = 0.f, C2a = 0.f, C2b = 0.f, Wa = 0.f, Wb = 0.f,
+          Da = 0.f, Db = 0.f;
+    uint32_t last0 = 0, last1 = 0;
 
     if (nb > 0 && tid == 0) issue(0);
     for (int b = 0; b < nb; b++) {
@@ -103,10 +117,10 @@ __global__ void __launch_bounds__(256) render_fwd(const RenderFwdParams p)
         mbar_wait(&s_full[s], (uint32_t)((b >> 1) & 1));
 
         for (int c0 = 0; c0 < cnt; c0 += 32) {
-            if (__all_sync(0xffffffffu, done)) break;
+            if (__all_sync(0xffffffffu, live == 0u)) break;
             const int r = c0 + lane;
             bool hit = false;
-            if (r < cnt) hit = rect_hit(s_q0[s][r], s_q1[s][r], fx0, fy0, 7.0f, 3.0f);
+            if (r < cnt) hit = rect_hit(s_q0[s][r], s_q1[s][r], fx0, fy0, 7.0f, 7.0f);
             uint32_t m = __ballot_sync(0xffffffffu, hit);
             while (m) {
                 const int j = __ffs(m) - 1;
@@ -114,68 +128,80 @@ __global__ void __launch_bounds__(256) render_fwd(const RenderFwdParams p)
                 const int rr = c0 + j;
                 const float4 a = s_q0[s][rr];
                 const float4 q = s_q1[s][rr];
-                bool contrib = false;
-                float uc_val = 0.0f;
+                bool cb0 = false, cb1 = false; // flashsplat: this pixel votes for this record
+                float uc0 = 0.0f, uc1 = 0.0f;
                 uint32_t gid = 0;
-                if (FLASH) gid = __float_as_uint(s_q2[s][rr].w);
-                bool gate = !done;
+                bool a0 = (live & 1u) != 0u, a1 = (live & 2u) != 0u;
                 if (FLASH) {
+                    gid = __float_as_uint(s_q2[s][rr].w);
                     if (p.unique_label != nullptr) { // FSR forward.cu:357-362
                         const int uid = __ldg(p.unique_label + gid);
-                        if (uid >= 0 && obj_id != uid) gate = false;
+                        if (uid >= 0 && obj0 != uid) a0 = false;
+                        if (uid >= 0 && obj1 != uid) a1 = false;
                     }
                 }
-                if (gate) {
-                    // DGR forward.cu:333-347, op order from the reference SASS
-                    const float dx = __fadd_rn(a.x, -pixfx), dy = __fadd_rn(a.y, -pixfy);
-                    const float t_zz = __fmul_rn(dy, __fmul_rn(dy, q.x));
-                    const float t_xx = __fmul_rn(dx, a.z);
-                    const float t_xy = __fmul_rn(dy, __fmul_rn(dx, a.w));
-                    const float power = __fmaf_rn(__fmaf_rn(dx, t_xx, t_zz), -0.5f, -t_xy);
-                    if (!(power > 0.0f)) {
-                        const float alpha = fminf(0.99f, __fmul_rn(q.y, expf(power)));
-                        if (!(alpha < 1.0f / 255.0f)) {
-                            const float test_T = __fmul_rn(T, __fadd_rn(1.0f, -alpha));
-                            if (test_T < 0.0001f) {
-                                done = true;
-                            } else {
-                                const float4 c = s_q2[s][rr];
-                                C0 = __fmaf_rn(T, __fmul_rn(alpha, c.x), C0);
-                                C1 = __fmaf_rn(T, __fmul_rn(alpha, c.y), C1);
-                                C2 = __fmaf_rn(T, __fmul_rn(alpha, c.z), C2);
-                                weight = __fmaf_rn(T, alpha, weight);
-                                D = __fmaf_rn(T, __fmul_rn(alpha, q.z), D);
-                                if (FLASH) {
-                                    contrib = obj_ok;
-                                    uc_val = __fmul_rn(alpha, T); // FSR forward.cu:398
-                                }
-                                T = test_T;
-                                last_contributor = (uint32_t)(b * RF_BATCH + rr + 1);
-                            }
-                        }
-                    }
+                // DGR forward.cu:333-353, op order from the reference SASS, two pixels at once.
+                // Straight-line: a pixel that fails a test carries on with alpha = 0 (branches
+                // here cost more than they skip, and their merges made ptxas copy every packed
+                // accumulator).
+                const float4 c = s_q2[s][rr];
+                const float dx = __fadd_rn(a.x, -pixfx);
+                const f2 dy = add2(bc2(a.y), npy);
+                const f2 t_zz = mul2(dy, mul2(dy, bc2(q.x)));
+                const float t_xx = __fmul_rn(dx, a.z);
+                const f2 nt_xy = mul2(dy, bc2(__fmul_rn(dx, -a.w))); // -(dy * (dx * B))
+                const f2 power = fma2(fma2(bc2(dx), bc2(t_xx), t_zz), bc2(-0.5f), nt_xy);
+                const f2 og = mul2(bc2(q.y), expf2(power));
+                const float al0 = fminf(0.99f, lo2(og)), al1 = fminf(0.99f, hi2(og));
+                a0 = a0 && !(lo2(power) > 0.0f) && !(al0 < 1.0f / 255.0f);
+                a1 = a1 && !(hi2(power) > 0.0f) && !(al1 < 1.0f / 255.0f);
+                const f2 T = pk2(Ta, Tb);
+                const f2 test_T = mul2(T, fma2(pk2(al0, al1), bc2(-1.0f), bc2(1.0f)));
+                const float tt0 = lo2(test_T), tt1 = hi2(test_T);
+                if (a0 && tt0 < 0.0001f) { live &= ~1u; a0 = false; }
+                if (a1 && tt1 < 0.0001f) { live &= ~2u; a1 = false; }
+                const f2 al = pk2(a0 ? al0 : 0.0f, a1 ? al1 : 0.0f);
+                const f2 C0 = fma2(T, mul2(al, bc2(c.x)), pk2(C0a, C0b));
+                const f2 C1 = fma2(T, mul2(al, bc2(c.y)), pk2(C1a, C1b));
+                const f2 C2 = fma2(T, mul2(al, bc2(c.z)), pk2(C2a, C2b));
+                const f2 Wt = fma2(T, al, pk2(Wa, Wb));
+                const f2 D = fma2(T, mul2(al, bc2(q.z)), pk2(Da, Db));
+                C0a = lo2(C0); C0b = hi2(C0); C1a = lo2(C1); C1b = hi2(C1); C2a = lo2(C2); C2b = hi2(C2);
+                Wa = lo2(Wt); Wb = hi2(Wt); Da = lo2(D); Db = hi2(D);
+                if (FLASH) {
+                    const f2 uc = mul2(al, T); // FSR forward.cu:398
+                    cb0 = a0 && ok0; cb1 = a1 && ok1;
+                    uc0 = lo2(uc); uc1 = hi2(uc);
                 }
+                Ta = a0 ? tt0 : Ta;
+                Tb = a1 ? tt1 : Tb;
+                const uint32_t pos = (uint32_t)(b * RF_BATCH + rr + 1);
+                if (a0) last0 = pos;
+                if (a1) last1 = pos;
                 if (FLASH) {
                     // per-(label, Gaussian) vote: one atomic per warp when the label is uniform
-                    const uint32_t cm = __ballot_sync(0xffffffffu, contrib);
+                    const uint32_t cm = __ballot_sync(0xffffffffu, cb0 || cb1);
                     if (cm) {
                         const int first = __ffs(cm) - 1;
-                        const int oid0 = __shfl_sync(0xffffffffu, obj_id, first);
-                        const uint32_t diff = __ballot_sync(0xffffffffu, contrib && obj_id != oid0);
+                        const int mine = cb0 ? obj0 : obj1;
+                        const int oid0 = __shfl_sync(0xffffffffu, mine, first);
+                        const uint32_t diff =
+                            __ballot_sync(0xffffffffu, (cb0 && obj0 != oid0) || (cb1 && obj1 != oid0));
                         if (diff == 0) {
-                            float v = contrib ? uc_val : 0.0f;
+                            float v = (cb0 ? uc0 : 0.0f) + (cb1 ? uc1 : 0.0f);
 #pragma unroll
                             for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
                             if (lane == 0) atomicAdd(p.used_count + (size_t)oid0 * p.P + gid, v);
-                        } else if (contrib) {
-                            atomicAdd(p.used_count + (size_t)obj_id * p.P + gid, uc_val);
+                        } else {
+                            if (cb0) atomicAdd(p.used_count + (size_t)obj0 * p.P + gid, uc0);
+                            if (cb1) atomicAdd(p.used_count + (size_t)obj1 * p.P + gid, uc1);
                         }
                     }
                 }
             }
         }
-        const int num_done = __syncthreads_count(done);
-        if (num_done == 256) {
+        const int num_done = __syncthreads_count(live == 0u);
+        if (num_done == RF_THREADS) {
             // a bulk copy for batch b+1 may still be in flight into this CTA's shared memory:
             // it must land before the CTA exits and the memory is handed to another CTA.
             if (b + 1 < nb && tid == 0) mbar_wait(&s_full[(b + 1) & 1], (uint32_t)(((b + 1) >> 1) & 1));
@@ -183,16 +209,29 @@ __global__ void __launch_bounds__(256) render_fwd(const RenderFwdParams p)
         }
     }
 
-    if (inside) {
-        const size_t HW = (size_t)p.H * p.W;
-        p.n_contrib[pix_id] = last_contributor;
-        // forward.cu:376-377: C + T * bg (contracted to one FMA in the reference build)
-        p.out_color[pix_id] = __fmaf_rn(__ldg(p.bg + 0), T, C0);
-        p.out_color[HW + pix_id] = __fmaf_rn(__ldg(p.bg + 1), T, C1);
-        p.out_color[2 * HW + pix_id] = __fmaf_rn(__ldg(p.bg + 2), T, C2);
-        p.out_alpha[pix_id] = weight;
-        p.out_depth[pix_id] = D;
-        if (FLASH) p.out_contrib_num[pix_id] = (int32_t)last_contributor;
+    const size_t HW = (size_t)p.H * p.W;
+    const float bg0 = __ldg(p.bg + 0), bg1 = __ldg(p.bg + 1), bg2 = __ldg(p.bg + 2);
+    // forward.cu:376-377: C + T * bg (contracted to one FMA in the reference build)
+    const f2 T = pk2(Ta, Tb), Wt = pk2(Wa, Wb), D = pk2(Da, Db);
+    const f2 o0 = fma2(bc2(bg0), T, pk2(C0a, C0b)), o1 = fma2(bc2(bg1), T, pk2(C1a, C1b)),
+             o2 = fma2(bc2(bg2), T, pk2(C2a, C2b));
+    if (in0) {
+        p.n_contrib[pix0] = last0;
+        p.out_color[pix0] = lo2(o0);
+        p.out_color[HW + pix0] = lo2(o1);
+        p.out_color[2 * HW + pix0] = lo2(o2);
+        p.out_alpha[pix0] = lo2(Wt);
+        p.out_depth[pix0] = lo2(D);
+        if (FLASH) p.out_contrib_num[pix0] = (int32_t)last0;
+    }
+    if (in1) {
+        p.n_contrib[pix1] = last1;
+        p.out_color[pix1] = hi2(o0);
+        p.out_color[HW + pix1] = hi2(o1);
+        p.out_color[2 * HW + pix1] = hi2(o2);
+        p.out_alpha[pix1] = hi2(Wt);
+        p.out_depth[pix1] = hi2(D);
+        if (FLASH) p.out_contrib_num[pix1] = (int32_t)last1;
     }
 }
 
@@ -214,9 +253,9 @@ int launch_render_fwd(const ws_view *v, int P, GeomState &gs, BinningState &bs, 
     p.num_obj = fl ? fl->num_obj : 0;
     dim3 grid((p.W + WS_BLOCK_X - 1) / WS_BLOCK_X, (p.H + WS_BLOCK_Y - 1) / WS_BLOCK_Y);
     if (fl)
-        render_fwd<true><<<grid, 256, 0, st>>>(p);
+        render_fwd<true><<<grid, RF_THREADS, 0, st>>>(p);
     else
-        render_fwd<false><<<grid, 256, 0, st>>>(p);
+        render_fwd<false><<<grid, RF_THREADS, 0, st>>>(p);
     WS_LAUNCH_CHECK(st, v->debug);
     return WS_OK;
 }
