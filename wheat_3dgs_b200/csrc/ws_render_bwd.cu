@@ -1,33 +1,43 @@
 // ws_render_bwd.cu -- backward of the alpha blending (replaces renderCUDA backward,
 // DGR backward.cu:415-601; flashsplat gate FSR backward.cu:455-462,529-536).
 //
-// Same tile / warp / lane mapping, record staging (TMA bulk copies, mbarrier double buffer) and
-// sub-tile culling as the forward (ws_render_fwd.cu), walking the tile's records back to front
-// from the largest last-contributor position in the tile (records behind it are never
-// fetched; the reference walks them with `contributor >= last_contributor -> continue`).
+// Same tile / warp / lane mapping (128 threads, warp = 8x8 pixels, two pixels per lane, packed
+// f32x2 arithmetic), record staging (TMA bulk copies, mbarrier double buffer) and sub-tile culling
+// as the forward (ws_render_fwd.cu), walking the tile's records back to front from the largest
+// last-contributor position in the tile (records behind it are never fetched; the reference
+// walks them with `contributor >= last_contributor -> continue`).  alpha is recomputed with the
+// forward's exact operations, so the set of contributing pairs is the forward's.
+//
+// Per-pixel recurrence.  The reference keeps, per pixel, the colour / depth / alpha accumulated
+// behind the current record (accum_rec, last_color, last_alpha ..., backward.cu:538-575) and
+// forms dL_dalpha = T * sum_ch (c_ch - accum_rec_ch) dL_ch + ... .  With
+//   dot_i = c_i . dL_dC + depth_i dL_dD + dL_dA   and   R_i = sum_{j behind i} alpha_j T_j dot_j
+// the same quantity is  dL_dalpha_i = T_i dot_i - (R_i + T_final bg . dL_dC) / (1 - alpha_i):
+// one scalar R per pixel instead of ten, accumulated back to front from small to large terms (no
+// cancellation).  T_i is recovered as in the reference, T_i = T_{i+1} / (1 - alpha_i).
 //
 // Gradient accumulation.  The reference issues 10 global float atomics per contributing
-// (pixel, Gaussian) pair (backward.cu:555,563,589-598).  Here the 32 pixels of a warp look at
-// the same record at the same time, so the 10 partial sums are first reduced across the warp
-// with transposing shuffle butterflies (an 8-slot tree, 9 shuffles, and a 2-slot tree, 5
-// shuffles: 44 instructions instead of the 62 of one 16-slot tree) and then 10 lanes issue ONE
-// red.global.add.f32 each into a 48-byte per-Gaussian accumulator row acc[g][12] (2 sectors).
-// (A shared-memory transpose was tried instead of the shuffles: fewer instructions, but the
-// SM-wide shared-memory pipe made it 5 % slower.)  Float summation order differs from the
-// reference's (non-deterministic) atomic order: gradients are in the 1e-3 relative tier.
+// (pixel, Gaussian) pair (backward.cu:555,563,589-598).  Here the 64 pixels of a warp look at
+// the same record at the same time: a lane adds its two pixels, the 10 partial sums are reduced
+// across the warp with transposing shuffle butterflies (an 8-slot tree, 9 shuffles, and a 2-slot
+// tree, 5 shuffles) and 10 lanes issue ONE red.global.add.f32 each into a 48-byte per-Gaussian
+// accumulator row acc[g][12] (2 sectors).  (A shared-memory transpose was tried instead of the
+// shuffles: fewer instructions, but the SM-wide shared-memory pipe made it 5 % slower.)  Float
+// summation order differs from the reference's (non-deterministic) atomic order: gradients are
+// in the 1e-3 relative tier.
 //
 // What is summed.  With g = G * dL_dalpha of a pair, every geometric gradient of the Gaussian is
 // a per-Gaussian constant times a pixel moment of g:  dL_dopacity = S g,
 // dL_dconic = -0.5 o (S g dx^2, S g dx dy, S g dy^2),  dL_dmean2D = -0.5 o (W (A S g dx + B S g dy),
 // H (C S g dy + B S g dx))  (backward.cu:583-598 with the constants factored out of the sums), so
 // the kernel accumulates {dL_dcolor rgb, dL_ddepth, S g dx, S g dy, S g dx^2, S g dx dy, S g dy^2, S g}
-// and preprocess_bwd applies the constants once per Gaussian.  The colour/depth/alpha
-// recurrences (backward.cu:538-575) are written as x += last_alpha * (y - x).
+// and preprocess_bwd applies the constants once per Gaussian.
 #include "ws_common.cuh"
 
 namespace ws {
 
 constexpr int RB_BATCH = 256;
+constexpr int RB_THREADS = 128;
 
 struct RenderBwdParams {
     const uint2 *ranges;
@@ -43,28 +53,30 @@ struct RenderBwdParams {
 };
 
 template <bool FLASH>
-__global__ void __launch_bounds__(256) render_bwd(const RenderBwdParams p)
+__global__ void __launch_bounds__(RB_THREADS) render_bwd(const RenderBwdParams p)
 {
     __shared__ __align__(128) float4 s_q0[2][RB_BATCH];
     __shared__ __align__(128) float4 s_q1[2][RB_BATCH];
     __shared__ __align__(128) float4 s_q2[2][RB_BATCH];
     __shared__ __align__(8) uint64_t s_full[2];
-    __shared__ uint32_t s_wmax[8];
+    __shared__ uint32_t s_wmax[RB_THREADS / 32];
 
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
     const uint32_t tile = blockIdx.y * gridDim.x + blockIdx.x;
     const int wx0 = blockIdx.x * WS_BLOCK_X + (w & 1) * 8;
-    const int wy0 = blockIdx.y * WS_BLOCK_Y + (w >> 1) * 4;
-    const int px = wx0 + (lane & 7), py = wy0 + (lane >> 3);
-    const bool inside = px < p.W && py < p.H;
-    const uint32_t pix_id = (uint32_t)p.W * py + px;
-    const float pixfx = (float)px, pixfy = (float)py;
+    const int wy0 = blockIdx.y * WS_BLOCK_Y + (w >> 1) * 8;
+    const int px = wx0 + (lane & 7), py0 = wy0 + (lane >> 3), py1 = py0 + 4;
+    const bool in0 = px < p.W && py0 < p.H, in1 = px < p.W && py1 < p.H;
+    const uint32_t pix0 = (uint32_t)p.W * py0 + px, pix1 = pix0 + 4u * (uint32_t)p.W;
+    const float pixfx = (float)px;
+    const f2 npy = pk2(-(float)py0, -(float)py1);
     const float fx0 = (float)wx0, fy0 = (float)wy0;
     const size_t HW = (size_t)p.H * p.W;
 
     const uint2 range = p.ranges[tile];
-    const uint32_t last = inside ? p.n_contrib[pix_id] : 0u; // 1-based position of last blended record
-    const uint32_t wmax = __reduce_max_sync(0xffffffffu, last);
+    // 1-based position of the last blended record (0 outside the image: nothing is active)
+    const uint32_t last0 = in0 ? p.n_contrib[pix0] : 0u, last1 = in1 ? p.n_contrib[pix1] : 0u;
+    const uint32_t wmax = __reduce_max_sync(0xffffffffu, max(last0, last1));
     if (lane == 0) s_wmax[w] = wmax;
     if (tid == 0) {
         mbar_init(&s_full[0], 1);
@@ -74,7 +86,7 @@ __global__ void __launch_bounds__(256) render_bwd(const RenderBwdParams p)
     __syncthreads();
     uint32_t bmax = 0;
 #pragma unroll
-    for (int k = 0; k < 8; k++) bmax = max(bmax, s_wmax[k]);
+    for (int k = 0; k < RB_THREADS / 32; k++) bmax = max(bmax, s_wmax[k]);
     const int n = (int)min(bmax, range.y - range.x); // records [0, n) of the tile matter
     const int nb = (n + RB_BATCH - 1) / RB_BATCH;
 
@@ -88,29 +100,32 @@ __global__ void __launch_bounds__(256) render_bwd(const RenderBwdParams p)
         tma_load_1d(&s_q2[s][0], p.q2 + off, bytes, &s_full[s]);
     };
 
-    // per-pixel state, DGR backward.cu:461-496
-    const float T_final = inside ? (1.0f - p.out_alpha[pix_id]) : 0.0f;
-    float T = T_final;
-    float dLr = 0.f, dLg = 0.f, dLb = 0.f, dLd = 0.f, dLa = 0.f;
-    if (inside) {
-        dLr = p.dL_dcolor[pix_id];
-        dLg = p.dL_dcolor[HW + pix_id];
-        dLb = p.dL_dcolor[2 * HW + pix_id];
-        dLd = p.dL_ddepth[pix_id];
-        dLa = p.dL_dalpha[pix_id];
+    // per-pixel constants, DGR backward.cu:461-496 (lo = pixel 0, hi = pixel 1)
+    const float Tf0 = in0 ? (1.0f - p.out_alpha[pix0]) : 0.0f, Tf1 = in1 ? (1.0f - p.out_alpha[pix1]) : 0.0f;
+    float dl0[5] = {0.f, 0.f, 0.f, 0.f, 0.f}, dl1[5] = {0.f, 0.f, 0.f, 0.f, 0.f};
+    if (in0) {
+        dl0[0] = p.dL_dcolor[pix0]; dl0[1] = p.dL_dcolor[HW + pix0]; dl0[2] = p.dL_dcolor[2 * HW + pix0];
+        dl0[3] = p.dL_ddepth[pix0]; dl0[4] = p.dL_dalpha[pix0];
     }
-    float bgdot = 0.0f;
-    bgdot += __ldg(p.bg + 0) * dLr;
-    bgdot += __ldg(p.bg + 1) * dLg;
-    bgdot += __ldg(p.bg + 2) * dLb;
-    const float nTf_bg = -T_final * bgdot; // background term of backward.cu:577-580, times 1/(1-alpha)
-    int obj_id = 0;
+    if (in1) {
+        dl1[0] = p.dL_dcolor[pix1]; dl1[1] = p.dL_dcolor[HW + pix1]; dl1[2] = p.dL_dcolor[2 * HW + pix1];
+        dl1[3] = p.dL_ddepth[pix1]; dl1[4] = p.dL_dalpha[pix1];
+    }
+    const f2 dLr = pk2(dl0[0], dl1[0]), dLg = pk2(dl0[1], dl1[1]), dLb = pk2(dl0[2], dl1[2]),
+             dLd = pk2(dl0[3], dl1[3]), dLa = pk2(dl0[4], dl1[4]);
+    const float bgr = __ldg(p.bg + 0), bgg = __ldg(p.bg + 1), bgb = __ldg(p.bg + 2);
+    // -T_final * (bg . dL_dpixel): the background term of backward.cu:577-580 before its 1/(1-alpha)
+    const f2 ntfbg = pk2(-Tf0 * (bgr * dl0[0] + bgg * dl0[1] + bgb * dl0[2]),
+                         -Tf1 * (bgr * dl1[0] + bgg * dl1[1] + bgb * dl1[2]));
+    int obj0 = 0, obj1 = 0;
     if (FLASH) {
-        if (inside && p.gt_mask) obj_id = __float2int_rz(p.gt_mask[pix_id]);
+        if (in0 && p.gt_mask) obj0 = __float2int_rz(p.gt_mask[pix0]);
+        if (in1 && p.gt_mask) obj1 = __float2int_rz(p.gt_mask[pix1]);
     }
-    // running "what lies behind" sums, backward.cu:538-575: x <- last_alpha*last_x + (1-last_alpha)*x
-    float last_alpha = 0.f, lc0 = 0.f, lc1 = 0.f, lc2 = 0.f, last_depth = 0.f;
-    float ac0 = 0.f, ac1 = 0.f, ac2 = 0.f, acd = 0.f, aca = 0.f;
+    // loop-carried state as scalar halves (packed at the point of use, see ws_render_fwd.cu):
+    // T = transmittance in front of the current record, R = sum over the records behind it of
+    // alpha_j T_j (c_j . dL_dC + depth_j dL_dD + dL_dA)
+    float Ta = Tf0, Tb = Tf1, Ra = 0.0f, Rb = 0.0f;
 
     if (nb > 0 && tid == 0) issue(nb - 1, 0);
     for (int it = 0; it < nb; it++) {
@@ -124,7 +139,7 @@ __global__ void __launch_bounds__(256) render_bwd(const RenderBwdParams p)
             const int r = c0 + lane;
             bool hit = false;
             if (r < cnt && (uint32_t)(b * RB_BATCH + r) < wmax)
-                hit = rect_hit(s_q0[s][r], s_q1[s][r], fx0, fy0, 7.0f, 3.0f);
+                hit = rect_hit(s_q0[s][r], s_q1[s][r], fx0, fy0, 7.0f, 7.0f);
             uint32_t m = __ballot_sync(0xffffffffu, hit);
             while (m) {
                 const int j = 31 - __clz(m);
@@ -135,51 +150,49 @@ __global__ void __launch_bounds__(256) render_bwd(const RenderBwdParams p)
                 const float4 q = s_q1[s][rr];
                 const float4 c = s_q2[s][rr];
                 const uint32_t gid = __float_as_uint(c.w);
-                float4 va = make_float4(0.f, 0.f, 0.f, 0.f), vb = make_float4(0.f, 0.f, 0.f, 0.f);
-                float2 vc = make_float2(0.f, 0.f);
-                bool act = inside && pos0 < last; // backward.cu:516-518
+                bool k0 = pos0 < last0, k1 = pos0 < last1; // backward.cu:516-518
                 if (FLASH) {
                     if (p.unique_label != nullptr) {
                         const int uid = __ldg(p.unique_label + gid);
-                        if (uid >= 0 && obj_id != uid) act = false;
+                        if (uid >= 0 && obj0 != uid) k0 = false;
+                        if (uid >= 0 && obj1 != uid) k1 = false;
                     }
                 }
-                bool contributed = false;
-                if (act) {
-                    const float dx = __fadd_rn(a.x, -pixfx), dy = __fadd_rn(a.y, -pixfy);
-                    const float t_zz = __fmul_rn(dy, __fmul_rn(dy, q.x));
-                    const float t_xx = __fmul_rn(dx, a.z);
-                    const float t_xy = __fmul_rn(dy, __fmul_rn(dx, a.w));
-                    const float power = __fmaf_rn(__fmaf_rn(dx, t_xx, t_zz), -0.5f, -t_xy);
-                    if (!(power > 0.0f)) {
-                        const float G = expf(power);
-                        const float alpha = fminf(0.99f, __fmul_rn(q.y, G));
-                        if (!(alpha < 1.0f / 255.0f)) {
-                            contributed = true;
-                            const float inv = rcp_approx(1.0f - alpha);
-                            T = T * inv; // backward.cu:534
-                            const float wgt = alpha * T;
-                            ac0 += last_alpha * (lc0 - ac0); lc0 = c.x;
-                            ac1 += last_alpha * (lc1 - ac1); lc1 = c.y;
-                            ac2 += last_alpha * (lc2 - ac2); lc2 = c.z;
-                            acd += last_alpha * (last_depth - acd); last_depth = q.z;
-                            aca += last_alpha * (1.0f - aca);
-                            last_alpha = alpha;
-                            float dL_dopa = (c.x - ac0) * dLr;
-                            dL_dopa += (c.y - ac1) * dLg;
-                            dL_dopa += (c.z - ac2) * dLb;
-                            dL_dopa += (q.z - acd) * dLd;
-                            dL_dopa += (1.0f - aca) * dLa;
-                            dL_dopa = dL_dopa * T + nTf_bg * inv;
-                            va = make_float4(wgt * dLr, wgt * dLg, wgt * dLb, wgt * dLd);
-                            const float g = G * dL_dopa;
-                            const float gx = g * dx, gy = g * dy;
-                            vb = make_float4(gx, gy, gx * dx, gx * dy);
-                            vc = make_float2(gy * dy, g);
-                        }
-                    }
-                }
-                if (__ballot_sync(0xffffffffu, contributed) == 0) continue;
+                // alpha exactly as the forward computed it (same ops, same order)
+                const float dx = __fadd_rn(a.x, -pixfx);
+                const f2 dy = add2(bc2(a.y), npy);
+                const f2 t_zz = mul2(dy, mul2(dy, bc2(q.x)));
+                const float t_xx = __fmul_rn(dx, a.z);
+                const f2 nt_xy = mul2(dy, bc2(__fmul_rn(dx, -a.w)));
+                const f2 power = fma2(fma2(bc2(dx), bc2(t_xx), t_zz), bc2(-0.5f), nt_xy);
+                const f2 G = expf2(power);
+                const f2 og = mul2(bc2(q.y), G);
+                const float al0 = fminf(0.99f, lo2(og)), al1 = fminf(0.99f, hi2(og));
+                k0 = k0 && !(lo2(power) > 0.0f) && !(al0 < 1.0f / 255.0f);
+                k1 = k1 && !(hi2(power) > 0.0f) && !(al1 < 1.0f / 255.0f);
+                if (__ballot_sync(0xffffffffu, k0 || k1) == 0) continue;
+                // a pixel that does not contribute runs along with alpha = 0 and G = 0: every
+                // sum below gets an exact zero from it and its T and R stay as they are
+                const f2 al = pk2(k0 ? al0 : 0.0f, k1 ? al1 : 0.0f);
+                const f2 Gm = pk2(k0 ? lo2(G) : 0.0f, k1 ? hi2(G) : 0.0f);
+                const f2 om = fma2(al, bc2(-1.0f), bc2(1.0f));
+                const f2 inv = pk2(rcp_approx(lo2(om)), rcp_approx(hi2(om)));
+                const f2 T = mul2(pk2(Ta, Tb), inv); // backward.cu:534
+                const f2 R = pk2(Ra, Rb);
+                const f2 dot = fma2(dLr, bc2(c.x), fma2(dLg, bc2(c.y), fma2(dLb, bc2(c.z), fma2(dLd, bc2(q.z), dLa))));
+                // dL_dalpha = T (c.dL) - (R + T_final bg.dL) / (1 - alpha)   (backward.cu:538-580)
+                const f2 dopa = fma2(T, dot, mul2(fma2(R, bc2(-1.0f), ntfbg), inv));
+                const f2 wgt = mul2(al, T);
+                const f2 Rn = fma2(wgt, dot, R);
+                Ta = k0 ? lo2(T) : Ta; Tb = k1 ? hi2(T) : Tb;
+                Ra = lo2(Rn); Rb = hi2(Rn);
+                const f2 cr = mul2(wgt, dLr), cg = mul2(wgt, dLg), cb = mul2(wgt, dLb), cd = mul2(wgt, dLd);
+                const f2 g = mul2(Gm, dopa);
+                const f2 gx = mul2(g, bc2(dx)), gy = mul2(g, dy);
+                const f2 gxx = mul2(gx, bc2(dx)), gxy = mul2(gx, dy), gyy = mul2(gy, dy);
+                const float4 va = make_float4(lo2(cr) + hi2(cr), lo2(cg) + hi2(cg), lo2(cb) + hi2(cb), lo2(cd) + hi2(cd));
+                const float4 vb = make_float4(lo2(gx) + hi2(gx), lo2(gy) + hi2(gy), lo2(gxx) + hi2(gxx), lo2(gxy) + hi2(gxy));
+                const float2 vc = make_float2(lo2(gyy) + hi2(gyy), lo2(g) + hi2(g));
                 {
                     // transposing butterfly over 8 slots (lane l ends with slot l>>2 summed over the warp)
                     float v[8] = {va.x, va.y, va.z, va.w, vb.x, vb.y, vb.z, vb.w};
@@ -243,9 +256,9 @@ int launch_render_bwd(const ws_view *v, int P, GeomState &gs, BinningState &bs, 
     p.unique_label = fl ? fl->unique_label : nullptr;
     dim3 grid((p.W + WS_BLOCK_X - 1) / WS_BLOCK_X, (p.H + WS_BLOCK_Y - 1) / WS_BLOCK_Y);
     if (fl && fl->unique_label)
-        render_bwd<true><<<grid, 256, 0, st>>>(p);
+        render_bwd<true><<<grid, RB_THREADS, 0, st>>>(p);
     else
-        render_bwd<false><<<grid, 256, 0, st>>>(p);
+        render_bwd<false><<<grid, RB_THREADS, 0, st>>>(p);
     WS_LAUNCH_CHECK(st, v->debug);
     return WS_OK;
 }
