@@ -22,6 +22,26 @@ def _deps():
     return d
 
 
+def build_variant(name, defines):
+    """A/B builds: wheat_3dgs_b200/variants/lib<name>.so compiled with -D<defines> (git-ignored, loaded through
+    WHEATSPLAT_LIB by tools/ab.py).  Not part of the product."""
+    vdir = os.path.join(HERE, "variants")
+    os.makedirs(os.path.join(vdir, name), exist_ok=True)
+    out = os.path.join(vdir, "lib%s.so" % name)
+    objs = []
+    for src in SOURCES:
+        obj = os.path.join(vdir, name, src.replace(".cu", ".o"))
+        cmd = [NVCC] + FLAGS + ["-D" + d for d in defines] + ["-c", os.path.join(CSRC, src), "-o", obj]
+        r = subprocess.run(cmd, capture_output=True, text=True)
+        if r.returncode != 0:
+            raise RuntimeError(r.stderr[-4000:])
+        objs.append(obj)
+    r = subprocess.run([NVCC, "-shared", "-o", out] + objs + ["-ccbin", "/usr/bin/g++"], capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError(r.stderr[-4000:])
+    return out
+
+
 def build(force=False, verbose=False, extra_flags=()):
     if not force and os.path.exists(LIB) and all(os.path.getmtime(LIB) >= os.path.getmtime(p) for p in _deps()):
         return LIB

@@ -1,7 +1,7 @@
 // ws_render_bwd.cu -- backward of the alpha blending (replaces renderCUDA backward,
 // DGR backward.cu:415-601; flashsplat gate FSR backward.cu:455-462,529-536).
 //
-// Same tile / warp / lane mapping (128 threads, warp = 8x8 pixels, two pixels per lane, packed
+// Same warp / lane mapping (warp = 8x8 pixels, two pixels per lane, packed
 // f32x2 arithmetic), record staging (TMA bulk copies, mbarrier double buffer) and sub-tile culling
 // as the forward (ws_render_fwd.cu), walking the tile's records back to front from the largest
 // last-contributor position in the tile (records behind it are never fetched; the reference
@@ -36,13 +36,20 @@
 
 namespace ws {
 
-constexpr int RB_BATCH = 256;
-constexpr int RB_THREADS = 128;
+#ifndef WS_RB_BATCH
+#define WS_RB_BATCH 128
+#endif
+#ifndef WS_RB_WARPS
+#define WS_RB_WARPS 2
+#endif
+constexpr int RB_BATCH = WS_RB_BATCH; // records per stage
+constexpr int RB_WARPS = WS_RB_WARPS;    // 8x8 pixel blocks (warps) per CTA: 1, 2 (a 16x8 half tile) or 4 (the tile)
+constexpr int RB_THREADS = 32 * RB_WARPS;
 
 struct RenderBwdParams {
     const uint2 *ranges;
     const float4 *q0, *q1, *q2;
-    int W, H;
+    int W, H, tiles_x;
     const float *bg;
     const float *out_alpha;
     const uint32_t *n_contrib;
@@ -59,12 +66,16 @@ __global__ void __launch_bounds__(RB_THREADS) render_bwd(const RenderBwdParams p
     __shared__ __align__(128) float4 s_q1[2][RB_BATCH];
     __shared__ __align__(128) float4 s_q2[2][RB_BATCH];
     __shared__ __align__(8) uint64_t s_full[2];
-    __shared__ uint32_t s_wmax[RB_THREADS / 32];
 
-    const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
-    const uint32_t tile = blockIdx.y * gridDim.x + blockIdx.x;
-    const int wx0 = blockIdx.x * WS_BLOCK_X + (w & 1) * 8;
-    const int wy0 = blockIdx.y * WS_BLOCK_Y + (w >> 1) * 8;
+    __shared__ uint32_t s_wmax[RB_WARPS];
+    const int lane = threadIdx.x & 31;
+    const bool leader = threadIdx.x == 0;
+    // the CTAs of a tile are adjacent in launch order
+    const uint32_t tile = blockIdx.x / (4 / RB_WARPS);
+    const uint32_t w = (blockIdx.x % (4 / RB_WARPS)) * RB_WARPS + (threadIdx.x >> 5);
+    const int tile_y = (int)(tile / (uint32_t)p.tiles_x), tile_x = (int)(tile - (uint32_t)tile_y * p.tiles_x);
+    const int wx0 = tile_x * WS_BLOCK_X + (int)(w & 1) * 8;
+    const int wy0 = tile_y * WS_BLOCK_Y + (int)(w >> 1) * 8;
     const int px = wx0 + (lane & 7), py0 = wy0 + (lane >> 3), py1 = py0 + 4;
     const bool in0 = px < p.W && py0 < p.H, in1 = px < p.W && py1 < p.H;
     const uint32_t pix0 = (uint32_t)p.W * py0 + px, pix1 = pix0 + 4u * (uint32_t)p.W;
@@ -77,17 +88,17 @@ __global__ void __launch_bounds__(RB_THREADS) render_bwd(const RenderBwdParams p
     // 1-based position of the last blended record (0 outside the image: nothing is active)
     const uint32_t last0 = in0 ? p.n_contrib[pix0] : 0u, last1 = in1 ? p.n_contrib[pix1] : 0u;
     const uint32_t wmax = __reduce_max_sync(0xffffffffu, max(last0, last1));
-    if (lane == 0) s_wmax[w] = wmax;
-    if (tid == 0) {
+    if (lane == 0) s_wmax[threadIdx.x >> 5] = wmax;
+    if (leader) {
         mbar_init(&s_full[0], 1);
         mbar_init(&s_full[1], 1);
         mbar_fence_init();
     }
-    __syncthreads();
+    if (RB_WARPS == 1) __syncwarp(); else __syncthreads();
     uint32_t bmax = 0;
 #pragma unroll
-    for (int k = 0; k < RB_THREADS / 32; k++) bmax = max(bmax, s_wmax[k]);
-    const int n = (int)min(bmax, range.y - range.x); // records [0, n) of the tile matter
+    for (int k = 0; k < RB_WARPS; k++) bmax = max(bmax, s_wmax[k]);
+    const int n = (int)min(bmax, range.y - range.x); // records [0, n) matter to this CTA
     const int nb = (n + RB_BATCH - 1) / RB_BATCH;
 
     auto issue = [&](int b, int s) {
@@ -127,12 +138,12 @@ __global__ void __launch_bounds__(RB_THREADS) render_bwd(const RenderBwdParams p
     // alpha_j T_j (c_j . dL_dC + depth_j dL_dD + dL_dA)
     float Ta = Tf0, Tb = Tf1, Ra = 0.0f, Rb = 0.0f;
 
-    if (nb > 0 && tid == 0) issue(nb - 1, 0);
+    if (nb > 0 && leader) issue(nb - 1, 0);
     for (int it = 0; it < nb; it++) {
         const int b = nb - 1 - it;
         const int s = it & 1;
         const int cnt = min(RB_BATCH, n - b * RB_BATCH);
-        if (it + 1 < nb && tid == 0) issue(b - 1, (it + 1) & 1);
+        if (it + 1 < nb && leader) issue(b - 1, (it + 1) & 1);
         mbar_wait(&s_full[s], (uint32_t)((it >> 1) & 1));
 
         for (int c0 = ((cnt - 1) >> 5) << 5; c0 >= 0; c0 -= 32) {
@@ -237,7 +248,7 @@ __global__ void __launch_bounds__(RB_THREADS) render_bwd(const RenderBwdParams p
                 }
             }
         }
-        __syncthreads(); // everyone is done with stage s before it is refilled
+        if (RB_WARPS == 1) __syncwarp(); else __syncthreads(); // stage s is free to be refilled
     }
 }
 
@@ -254,7 +265,8 @@ int launch_render_bwd(const ws_view *v, int P, GeomState &gs, BinningState &bs, 
     p.acc = gs.acc;
     p.gt_mask = fl ? fl->gt_mask : nullptr;
     p.unique_label = fl ? fl->unique_label : nullptr;
-    dim3 grid((p.W + WS_BLOCK_X - 1) / WS_BLOCK_X, (p.H + WS_BLOCK_Y - 1) / WS_BLOCK_Y);
+    p.tiles_x = (p.W + WS_BLOCK_X - 1) / WS_BLOCK_X;
+    const unsigned grid = (unsigned)(4 / RB_WARPS) * (unsigned)p.tiles_x * (unsigned)((p.H + WS_BLOCK_Y - 1) / WS_BLOCK_Y);
     if (fl && fl->unique_label)
         render_bwd<true><<<grid, RB_THREADS, 0, st>>>(p);
     else

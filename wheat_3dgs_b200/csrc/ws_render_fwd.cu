@@ -1,7 +1,9 @@
 // ws_render_fwd.cu -- forward alpha blending (replaces renderCUDA, DGR forward.cu:261-381, and
 // the flashsplat variant FSR forward.cu:269-418).
 //
-// One CTA per 16x16 tile, 128 threads; warp w owns the 8x8 pixel block
+// One CTA per 16x16 tile, 128 threads (WS_RF_WARPS = 4; 2 or 1 warps per CTA split the tile into
+// adjacent CTAs that each stage the tile's records -- all within 3 % of each other on B200, the
+// kernel is instruction-issue bound); warp w owns the 8x8 pixel block
 // (x0 + (w&1)*8 .. +7, y0 + (w>>1)*8 .. +7) and every lane TWO pixels of it, (l&7, l>>3) and
 // (l&7, (l>>3)+4).  The two pixels share dx, so the per-pair arithmetic runs as packed f32x2
 // instructions (FADD2/FMUL2/FFMA2, sm_100: one issue slot does both pixels, scalar operands
@@ -29,18 +31,25 @@
 //
 // Early termination: a pixel stops when T would fall below 1e-4 (forward.cu:348-353); a warp
 // leaves a batch when all 64 pixels are done (warp vote); the CTA stops fetching when
-// __syncthreads_count says all 128 threads are done (forward.cu:305-308).
+// all its threads are done (forward.cu:305-308).
 #include "ws_common.cuh"
 
 namespace ws {
 
-constexpr int RF_BATCH = 256;
-constexpr int RF_THREADS = 128;
+#ifndef WS_RF_BATCH
+#define WS_RF_BATCH 256
+#endif
+#ifndef WS_RF_WARPS
+#define WS_RF_WARPS 4
+#endif
+constexpr int RF_BATCH = WS_RF_BATCH; // records per stage
+constexpr int RF_WARPS = WS_RF_WARPS;    // 8x8 pixel blocks (warps) per CTA: 1, 2 (a 16x8 half tile) or 4 (the tile)
+constexpr int RF_THREADS = 32 * RF_WARPS;
 
 struct RenderFwdParams {
     const uint2 *ranges;
     const float4 *q0, *q1, *q2;
-    int W, H, P;
+    int W, H, P, tiles_x;
     const float *bg;
     float *out_color, *out_depth, *out_alpha;
     uint32_t *n_contrib;
@@ -60,11 +69,14 @@ __global__ void __launch_bounds__(RF_THREADS) render_fwd(const RenderFwdParams p
     __shared__ __align__(128) float4 s_q2[2][RF_BATCH];
     __shared__ __align__(8) uint64_t s_full[2];
 
-    const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
-    const int tiles_x = gridDim.x;
-    const uint32_t tile = blockIdx.y * tiles_x + blockIdx.x;
-    const int wx0 = blockIdx.x * WS_BLOCK_X + (w & 1) * 8;
-    const int wy0 = blockIdx.y * WS_BLOCK_Y + (w >> 1) * 8;
+    const int lane = threadIdx.x & 31;
+    const bool leader = threadIdx.x == 0;
+    // the CTAs of a tile are adjacent in launch order
+    const uint32_t tile = blockIdx.x / (4 / RF_WARPS);
+    const uint32_t w = (blockIdx.x % (4 / RF_WARPS)) * RF_WARPS + (threadIdx.x >> 5);
+    const int tile_y = (int)(tile / (uint32_t)p.tiles_x), tile_x = (int)(tile - (uint32_t)tile_y * p.tiles_x);
+    const int wx0 = tile_x * WS_BLOCK_X + (int)(w & 1) * 8;
+    const int wy0 = tile_y * WS_BLOCK_Y + (int)(w >> 1) * 8;
     const int px = wx0 + (lane & 7), py0 = wy0 + (lane >> 3), py1 = py0 + 4;
     const bool in0 = px < p.W && py0 < p.H, in1 = px < p.W && py1 < p.H;
     const uint32_t pix0 = (uint32_t)p.W * py0 + px, pix1 = pix0 + 4u * (uint32_t)p.W;
@@ -76,12 +88,12 @@ __global__ void __launch_bounds__(RF_THREADS) render_fwd(const RenderFwdParams p
     const int n = (int)(range.y - range.x);
     const int nb = (n + RF_BATCH - 1) / RF_BATCH;
 
-    if (tid == 0) {
+    if (leader) {
         mbar_init(&s_full[0], 1);
         mbar_init(&s_full[1], 1);
         mbar_fence_init();
     }
-    __syncthreads();
+    if (RF_WARPS == 1) __syncwarp(); else __syncthreads();
 
     auto issue = [&](int b) {
         const int s = b & 1;
@@ -109,11 +121,11 @@ __global__ void __launch_bounds__(RF_THREADS) render_fwd(const RenderFwdParams p
           Da = 0.f, Db = 0.f;
     uint32_t last0 = 0, last1 = 0;
 
-    if (nb > 0 && tid == 0) issue(0);
+    if (nb > 0 && leader) issue(0);
     for (int b = 0; b < nb; b++) {
         const int s = b & 1;
         const int cnt = min(RF_BATCH, n - b * RF_BATCH);
-        if (b + 1 < nb && tid == 0) issue(b + 1); // stage (b+1)&1 was released by the barrier below
+        if (b + 1 < nb && leader) issue(b + 1); // stage (b+1)&1 was released by the vote below
         mbar_wait(&s_full[s], (uint32_t)((b >> 1) & 1));
 
         for (int c0 = 0; c0 < cnt; c0 += 32) {
@@ -200,11 +212,13 @@ __global__ void __launch_bounds__(RF_THREADS) render_fwd(const RenderFwdParams p
                 }
             }
         }
-        const int num_done = __syncthreads_count(live == 0u);
-        if (num_done == RF_THREADS) {
+        // all lanes are through with stage s (the vote orders their reads before the refill)
+        const bool all_done = RF_WARPS == 1 ? (__all_sync(0xffffffffu, live == 0u) != 0)
+                                            : (__syncthreads_and(live == 0u) != 0);
+        if (all_done) {
             // a bulk copy for batch b+1 may still be in flight into this CTA's shared memory:
             // it must land before the CTA exits and the memory is handed to another CTA.
-            if (b + 1 < nb && tid == 0) mbar_wait(&s_full[(b + 1) & 1], (uint32_t)(((b + 1) >> 1) & 1));
+            if (b + 1 < nb && leader) mbar_wait(&s_full[(b + 1) & 1], (uint32_t)(((b + 1) >> 1) & 1));
             break;
         }
     }
@@ -251,7 +265,8 @@ int launch_render_fwd(const ws_view *v, int P, GeomState &gs, BinningState &bs, 
     p.used_count = fl ? fl->used_count : nullptr;
     p.out_contrib_num = fl ? fl->out_contrib_num : nullptr;
     p.num_obj = fl ? fl->num_obj : 0;
-    dim3 grid((p.W + WS_BLOCK_X - 1) / WS_BLOCK_X, (p.H + WS_BLOCK_Y - 1) / WS_BLOCK_Y);
+    p.tiles_x = (p.W + WS_BLOCK_X - 1) / WS_BLOCK_X;
+    const unsigned grid = (unsigned)(4 / RF_WARPS) * (unsigned)p.tiles_x * (unsigned)((p.H + WS_BLOCK_Y - 1) / WS_BLOCK_Y);
     if (fl)
         render_fwd<true><<<grid, RF_THREADS, 0, st>>>(p);
     else

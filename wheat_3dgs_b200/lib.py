@@ -7,7 +7,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libwheatsplat.so")
+# WHEATSPLAT_LIB: another build of the same library (A/B timing of kernel variants, tools/ab.sh)
+LIB_PATH = os.environ.get("WHEATSPLAT_LIB") or os.path.join(_HERE, "libwheatsplat.so")
 
 WS_ABI_VERSION = 1
 
