@@ -59,6 +59,8 @@ class ClockSampler:
         self.index, self.proc, self.lines = index, None, []
 
     def start(self):
+        if os.environ.get("WS_NO_CLOCKS"):
+            return
         try:
             self.proc = subprocess.Popen(
                 ["nvidia-smi", "--query-gpu=" + self.Q, "--format=csv,noheader,nounits", "-i", str(self.index),
@@ -71,6 +73,13 @@ class ClockSampler:
     def _pump(self):
         for ln in self.proc.stdout:
             self.lines.append((time.time(), ln.strip()))
+
+    def wait_started(self, n=2, timeout=5.0):
+        """nvidia-smi takes a while to attach and holds up CUDA API calls while it does: the timed region
+        must not start before it is polling steadily."""
+        t0 = time.time()
+        while self.proc is not None and len(self.lines) < n and time.time() - t0 < timeout:
+            time.sleep(0.02)
 
     def stop(self, t0=None, t1=None):
         if self.proc is None:
@@ -251,7 +260,7 @@ def run_ours(args, rank, world, local):
     barrier()
     clk = ClockSampler(local)
     clk.start()
-    time.sleep(0.25)
+    clk.wait_started()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     n0 = ops.launch_count()
     t0 = time.time()
@@ -366,7 +375,7 @@ def run_reference_cuda(args, local):
     torch.cuda.synchronize()
     clk = ClockSampler(local)
     clk.start()
-    time.sleep(0.25)
+    clk.wait_started()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     t0 = time.time()
     e0.record()

@@ -78,6 +78,15 @@ static cudaEvent_t total_event()
     return ev[dev];
 }
 
+// pinned landing word for num_rendered: a D2H copy into pageable memory blocks the host until
+// the stream has drained, a copy into pinned memory is asynchronous
+static uint32_t *total_host()
+{
+    static thread_local uint32_t *p = nullptr;
+    if (!p && cudaHostAlloc((void **)&p, 64, cudaHostAllocDefault) != cudaSuccess) p = nullptr;
+    return p;
+}
+
 // DGR rasterizer_impl.cu:35-50
 static uint32_t get_higher_msb(uint32_t n)
 {
@@ -202,8 +211,9 @@ extern "C" int64_t ws_forward_prepare(const ws_view *view, const ws_gaussians *g
     if (rc != WS_OK) return rc;
     { ProfScope ps(1, st); rc = launch_scan_blocks(g->P, gs, st, view->debug != 0); }
     if (rc != WS_OK) return rc;
-    uint32_t total = 0;
-    WS_CUDA_CHECK(cudaMemcpyAsync(&total, gs.total, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+    uint32_t *th = total_host();
+    if (!th) { set_error("ws_forward_prepare: cudaHostAlloc failed"); return WS_E_CUDA; }
+    WS_CUDA_CHECK(cudaMemcpyAsync(th, gs.total, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
     if (!binning_keys64()) {
         // the depth sort needs nothing from the host: it runs while the host waits for `total`
         // and sizes the binning scratch (the reference idles the GPU there, rasterizer_impl.cu:282)
@@ -215,7 +225,7 @@ extern "C" int64_t ws_forward_prepare(const ws_view *view, const ws_gaussians *g
     } else {
         WS_CUDA_CHECK(cudaStreamSynchronize(st));
     }
-    return (int64_t)total;
+    return (int64_t)*th;
 }
 
 extern "C" int ws_forward_render(const ws_view *view, const ws_gaussians *g, const int32_t *radii, void *geom,

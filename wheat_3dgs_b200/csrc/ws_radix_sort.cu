@@ -33,7 +33,15 @@ constexpr uint32_t RS_FLAG_AGG = 1u << 30; // tile aggregate available
 constexpr uint32_t RS_FLAG_INC = 2u << 30; // inclusive prefix available
 constexpr uint32_t RS_VAL_MASK = (1u << 30) - 1;
 
-size_t sort_tiles(size_t n) { return (n + RS_TILE - 1) / RS_TILE; }
+// Pairs per thread.  (4 for small inputs -- more CTAs per SM for the 1 M-pair depth sort -- was
+// measured slower, 25 vs 20 us per pass: a single-wave pass is bound by the look-back chain, which
+// grows with the number of tiles.)
+static inline int sort_items(size_t n) { (void)n; return RS_ITEMS; }
+size_t sort_tiles(size_t n)
+{
+    const size_t t = (size_t)RS_THREADS * sort_items(n);
+    return (n + t - 1) / t;
+}
 
 SortScratch SortScratch::from(char *&p, size_t n)
 {
@@ -108,48 +116,35 @@ __device__ __forceinline__ void st_relaxed(uint32_t *p, uint32_t v)
     asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 
-template <typename K>
-__global__ void __launch_bounds__(RS_THREADS, sizeof(K) == 4 ? 4 : 3)
-rs_onesweep(const K *__restrict__ keys_in, K *__restrict__ keys_out,
-            const uint32_t *__restrict__ vals_in, uint32_t *__restrict__ vals_out, size_t n, int shift,
-            int bits, const uint32_t *__restrict__ bins, uint32_t *__restrict__ counter,
-            uint32_t *__restrict__ status)
+// One tile of one pass.  FULL = all 256*ITEMS slots of the tile hold pairs (every tile but the
+// last): no bounds checks, which otherwise cost a 64-bit compare per access.
+template <typename K, int ITEMS, bool FULL>
+__device__ __forceinline__ void rs_tile_body(const K *__restrict__ kin, const uint32_t *__restrict__ vin,
+                                             K *__restrict__ keys_out, uint32_t *__restrict__ vals_out,
+                                             uint32_t nt, uint32_t tile, int shift, uint32_t mask,
+                                             const uint32_t *__restrict__ bins, uint32_t *__restrict__ status,
+                                             K *s_keys, uint32_t *s_vals, uint32_t (*s_whist)[256],
+                                             uint32_t *s_dstart, uint32_t *s_goff, uint32_t *s_w)
 {
-    __shared__ K s_keys[RS_TILE];                 // 24 KB (u64) / 12 KB (u32)
-    __shared__ uint32_t s_vals[RS_TILE];          // 12 KB
-    __shared__ uint32_t s_whist[RS_WARPS][256];   //  8 KB
-    __shared__ uint32_t s_dstart[256];
-    __shared__ uint32_t s_goff[256];
-    __shared__ uint32_t s_w[RS_WARPS];
-    __shared__ uint32_t s_tile;
-
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
-    const uint32_t mask = (1u << bits) - 1u;
     const uint32_t lt_mask = (1u << lane) - 1u;
+    const uint32_t o0 = (uint32_t)w * (ITEMS * 32) + lane; // tile-local slot of item 0 (warp-striped)
 
-    if (tid == 0) s_tile = atomicAdd(counter, 1u);
+    K key[ITEMS];
+    uint32_t val[ITEMS];
+    uint32_t rank[ITEMS];
 #pragma unroll
-    for (int k = 0; k < RS_WARPS; k++) s_whist[k][tid] = 0;
-    __syncthreads();
-    const uint32_t tile = s_tile;
-    const size_t base = (size_t)tile * RS_TILE;
-    const size_t seg = base + (size_t)w * (RS_ITEMS * 32);
-
-    K key[RS_ITEMS];
-    uint32_t val[RS_ITEMS];
-    uint32_t rank[RS_ITEMS];
-#pragma unroll
-    for (int i = 0; i < RS_ITEMS; i++) {
-        const size_t idx = seg + (size_t)i * 32 + lane;
-        const bool valid = idx < n;
-        key[i] = valid ? keys_in[idx] : (K)~(K)0;
-        val[i] = valid ? vals_in[idx] : 0u;
+    for (int i = 0; i < ITEMS; i++) {
+        const uint32_t o = o0 + i * 32;
+        const bool valid = FULL || o < nt;
+        key[i] = valid ? kin[o] : (K)~(K)0;
+        val[i] = valid ? vin[o] : 0u;
     }
 
     // ---- rank inside the warp, item by item (stable) ----
 #pragma unroll
-    for (int i = 0; i < RS_ITEMS; i++) {
-        const bool valid = (seg + (size_t)i * 32 + lane) < n;
+    for (int i = 0; i < ITEMS; i++) {
+        const bool valid = FULL || (o0 + i * 32) < nt;
         const uint32_t d = valid ? ((uint32_t)(key[i] >> shift) & mask) : 0x100u;
         const uint32_t peers = __match_any_sync(0xffffffffu, d);
         uint32_t pre = 0;
@@ -206,8 +201,8 @@ rs_onesweep(const K *__restrict__ keys_in, K *__restrict__ keys_out,
 
     // ---- scatter into shared memory in sorted order ----
 #pragma unroll
-    for (int i = 0; i < RS_ITEMS; i++) {
-        const bool valid = (seg + (size_t)i * 32 + lane) < n;
+    for (int i = 0; i < ITEMS; i++) {
+        const bool valid = FULL || (o0 + i * 32) < nt;
         if (valid) {
             const uint32_t d = (uint32_t)(key[i] >> shift) & mask;
             const uint32_t pos = s_dstart[d] + s_whist[w][d] + rank[i];
@@ -218,18 +213,50 @@ rs_onesweep(const K *__restrict__ keys_in, K *__restrict__ keys_out,
     __syncthreads();
 
     // ---- write out: consecutive positions of one digit are consecutive in global memory ----
-    const uint32_t ntile = (uint32_t)min((size_t)RS_TILE, n - base);
 #pragma unroll
-    for (int j = 0; j < RS_ITEMS; j++) {
+    for (int j = 0; j < ITEMS; j++) {
         const uint32_t p = tid + j * RS_THREADS;
-        if (p < ntile) {
+        if (FULL || p < nt) {
             const K k = s_keys[p];
             const uint32_t d = (uint32_t)(k >> shift) & mask;
-            const size_t dst = (size_t)(s_goff[d] + p);
+            const uint32_t dst = s_goff[d] + p; // < n < 2^30
             keys_out[dst] = k;
             vals_out[dst] = s_vals[p];
         }
     }
+}
+
+template <typename K, int ITEMS>
+__global__ void __launch_bounds__(RS_THREADS, sizeof(K) == 4 ? 4 : 3)
+rs_onesweep(const K *__restrict__ keys_in, K *__restrict__ keys_out,
+            const uint32_t *__restrict__ vals_in, uint32_t *__restrict__ vals_out, size_t n, int shift,
+            int bits, const uint32_t *__restrict__ bins, uint32_t *__restrict__ counter,
+            uint32_t *__restrict__ status)
+{
+    constexpr int TILE = RS_THREADS * ITEMS;
+    __shared__ K s_keys[TILE];
+    __shared__ uint32_t s_vals[TILE];
+    __shared__ uint32_t s_whist[RS_WARPS][256]; // 8 KB
+    __shared__ uint32_t s_dstart[256];
+    __shared__ uint32_t s_goff[256];
+    __shared__ uint32_t s_w[RS_WARPS];
+    __shared__ uint32_t s_tile;
+
+    const int tid = threadIdx.x;
+    if (tid == 0) s_tile = atomicAdd(counter, 1u); // ticket: predecessors are always resident
+#pragma unroll
+    for (int k = 0; k < RS_WARPS; k++) s_whist[k][tid] = 0;
+    __syncthreads();
+    const uint32_t tile = s_tile;
+    const size_t base = (size_t)tile * TILE;
+    const uint32_t nt = (uint32_t)min((size_t)TILE, n - base);
+    const uint32_t mask = (1u << bits) - 1u;
+    if (nt == (uint32_t)TILE)
+        rs_tile_body<K, ITEMS, true>(keys_in + base, vals_in + base, keys_out, vals_out, nt, tile, shift, mask, bins,
+                                     status, s_keys, s_vals, s_whist, s_dstart, s_goff, s_w);
+    else
+        rs_tile_body<K, ITEMS, false>(keys_in + base, vals_in + base, keys_out, vals_out, nt, tile, shift, mask, bins,
+                                      status, s_keys, s_vals, s_whist, s_dstart, s_goff, s_w);
 }
 
 template <typename K>
@@ -262,8 +289,12 @@ static int sort_pairs_impl(size_t n, K *keys_in, K *keys_out, uint32_t *vals_in,
     uint32_t *vi = vals_in, *vo = vals_out;
     for (int p = 0; p < npass; p++) {
         const int bits = end_bit - 8 * p < 8 ? end_bit - 8 * p : 8;
-        rs_onesweep<K><<<(unsigned)nt, RS_THREADS, 0, st>>>(ki, ko, vi, vo, n, 8 * p, bits, ss.hist + p * 256,
-                                                         ss.counters + p, ss.status + (size_t)p * nt * 256);
+        if (sort_items(n) == 4)
+            rs_onesweep<K, 4><<<(unsigned)nt, RS_THREADS, 0, st>>>(ki, ko, vi, vo, n, 8 * p, bits, ss.hist + p * 256,
+                                                                  ss.counters + p, ss.status + (size_t)p * nt * 256);
+        else
+            rs_onesweep<K, RS_ITEMS><<<(unsigned)nt, RS_THREADS, 0, st>>>(
+                ki, ko, vi, vo, n, 8 * p, bits, ss.hist + p * 256, ss.counters + p, ss.status + (size_t)p * nt * 256);
         WS_LAUNCH_CHECK(st, debug);
         K *tk = ki; ki = ko; ko = tk;
         uint32_t *tv = vi; vi = vo; vo = tv;
