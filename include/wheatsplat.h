@@ -153,6 +153,21 @@ int ws_knn_dist2(int32_t P, const float *points, float *mean_dists, void *scratc
 int ws_multi_instance_opt(int32_t num_rows, int32_t P, const float *all_contrib, float gamma,
                           uint8_t *labels, ws_stream_t stream);
 
+/* Training loss either side of the rasterizer (replaces utils/loss_utils.py:17-62
+ * as used by train_vanilla_3dgs.py:77-80): per image plane (= batch x channel, img/gt float
+ * [planes,H,W]) the sum of the SSIM map (11x11 Gaussian window, sigma 1.5, zero padding) and the
+ * sum of |img - gt|.  sums: float[planes][2] = {sum ssim, sum |img-gt|}.  The forward leaves the
+ * three partial-derivative maps the backward convolves in `scratch` (ws_loss_bytes), which the
+ * caller keeps until the backward.
+ * Backward: dL_dimg = a * d(sum ssim)/dimg + b * d(sum |img-gt|)/dimg with {a, b} read from the
+ * device array coef (float[2], or float[planes][2] when per_plane != 0). */
+size_t ws_loss_bytes(int32_t planes, int32_t height, int32_t width);
+int ws_l1_ssim_forward(int32_t planes, int32_t height, int32_t width, const float *img, const float *gt,
+                       float *sums, void *scratch, size_t scratch_bytes, ws_stream_t stream);
+int ws_l1_ssim_backward(int32_t planes, int32_t height, int32_t width, const float *img, const float *gt,
+                        const float *coef, int32_t per_plane, const void *scratch, size_t scratch_bytes,
+                        float *dL_dimg, ws_stream_t stream);
+
 /* The stable LSD radix sort the rasterizer uses (replaces cub::DeviceRadixSort::SortPairs,
  * rasterizer_impl.cu:304-309), exposed for parity tests: sorts (u64 key, u32 value) pairs on
  * key bits [0, end_bit).  Results land in keys_out / vals_out; *_in are clobbered. */

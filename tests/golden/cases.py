@@ -85,6 +85,34 @@ def votes_inputs():
     return a
 
 
+# name: (shape, lambda_dssim).  Images are smooth blobs + noise in [0,1]; "ragged" is not a multiple of the
+# loss kernels' 32x32 tile and smaller than the 11x11 window's halo on one side; "batch" is 4-D.
+LOSS_CASES = {
+    "rgb": ((3, 96, 128), 0.2),
+    "ragged": ((3, 37, 75), 0.2),
+    "tiny": ((1, 7, 5), 0.5),
+    "batch": ((2, 3, 40, 48), 0.2),
+}
+
+
+def loss_inputs(name):
+    shape, lam = LOSS_CASES[name]
+    rng = np.random.default_rng(len(name) * 1000 + shape[-1])
+    H, W = shape[-2], shape[-1]
+    yy, xx = np.mgrid[0:H, 0:W].astype(np.float64)
+    planes = int(np.prod(shape[:-2]))
+    gt = np.zeros((planes, H, W))
+    for p in range(planes):
+        for _ in range(6):
+            cx, cy, r = rng.uniform(0, W), rng.uniform(0, H), rng.uniform(2, max(3, W / 4))
+            gt[p] += rng.uniform(0.1, 0.6) * np.exp(-((xx - cx) ** 2 + (yy - cy) ** 2) / (2 * r * r))
+    gt = np.clip(gt + rng.normal(0, 0.02, gt.shape), 0, 1)
+    img = np.clip(gt + rng.normal(0, 0.08, gt.shape) + 0.05, 0, 1)
+    # some exactly equal pixels: torch.abs has gradient sign(0) = 0 there
+    img[:, ::5, ::7] = gt[:, ::5, ::7]
+    return img.reshape(shape).astype(np.float32), gt.reshape(shape).astype(np.float32), lam
+
+
 def input_hash(arrays):
     h = hashlib.sha256()
     for a in arrays:

@@ -109,3 +109,21 @@ def test_empty_and_fully_culled_scene():
     H, W = cam["image_height"], cam["image_width"]
     assert_image("color", of["out_color"], np.broadcast_to(cases.BG[:, None, None], (3, H, W)))
     assert not of["out_alpha"].any()
+
+
+@pytest.mark.parametrize("name", sorted(cases.LOSS_CASES))
+def test_loss_oracle_matches_reference_python(golden_dir, name):
+    """oracle/loss_oracle.py against the reference's own utils/loss_utils.py + autograd on CPU
+    (tests/golden/make_golden_loss.py)."""
+    import loss_oracle
+    gold = _load(golden_dir, "loss_" + name)
+    img, gt, lam = cases.loss_inputs(name)
+    _check_inputs(gold, [img, gt])
+    o = loss_oracle.loss_and_grad(img, gt, lam)
+    assert abs(o["loss"] - float(gold["loss"])) <= 2e-6
+    assert abs(o["l1"] - float(gold["l1"])) <= 2e-6
+    assert abs(o["ssim"] - float(gold["ssim"])) <= 1e-5
+    assert_grad("dloss/dimage", o["grad"], gold["grad"])
+    if "ssim_per_image" in gold.files:
+        per = o["ssim_per_plane"].reshape(img.shape[0], -1).mean(axis=1)
+        assert np.abs(per - gold["ssim_per_image"]).max() <= 1e-5

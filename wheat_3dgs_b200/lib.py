@@ -16,7 +16,8 @@ WS_ABI_VERSION = 1
 SYMBOLS = [
     "ws_abi_version", "ws_last_error", "ws_geom_bytes", "ws_image_bytes", "ws_binning_bytes",
     "ws_forward_prepare", "ws_forward_render", "ws_backward", "ws_mark_visible", "ws_knn_bytes",
-    "ws_knn_dist2", "ws_multi_instance_opt", "ws_sort_bytes", "ws_sort_pairs_u64", "ws_sort_pairs_u32", "ws_set_binning_mode", "ws_debug_fetch",
+    "ws_knn_dist2", "ws_multi_instance_opt", "ws_sort_bytes", "ws_sort_pairs_u64", "ws_sort_pairs_u32", "ws_set_binning_mode",
+    "ws_loss_bytes", "ws_l1_ssim_forward", "ws_l1_ssim_backward", "ws_debug_fetch",
     "ws_launch_count", "ws_prof_enable", "ws_prof_read", "ws_prof_stage_name", "ws_debug_count_pairs",
 ]
 WS_PROF_NSTAGES = 8
@@ -99,6 +100,12 @@ def load():
     lib.ws_sort_bytes.argtypes = [i64]
     lib.ws_sort_pairs_u64.restype = C.c_int
     lib.ws_sort_pairs_u64.argtypes = [i64, vp, vp, vp, vp, i32, vp, sz, vp]
+    lib.ws_loss_bytes.restype = sz
+    lib.ws_loss_bytes.argtypes = [i32, i32, i32]
+    lib.ws_l1_ssim_forward.restype = C.c_int
+    lib.ws_l1_ssim_forward.argtypes = [i32, i32, i32, vp, vp, vp, vp, sz, vp]
+    lib.ws_l1_ssim_backward.restype = C.c_int
+    lib.ws_l1_ssim_backward.argtypes = [i32, i32, i32, vp, vp, vp, i32, vp, sz, vp, vp]
     lib.ws_set_binning_mode.restype = C.c_int
     lib.ws_set_binning_mode.argtypes = [i32]
     lib.ws_sort_pairs_u32.restype = C.c_int
