@@ -523,18 +523,24 @@ def main():
             d["tflops"] = fl[name] / 1e12 / (per * 1e-3) if per > 0 else None
         stages[name] = d
     top = max(stages, key=lambda k: stages[k]["ms_per_view"])
+    traffic = None  # DRAM bytes per launch of the dominant kernel, from the committed ncu --set full capture
+    try:
+        with open(os.path.join(ROOT, "profiles", "r01_traffic.json")) as f:
+            traffic = json.load(f)["bytes_per_launch"].get(top) if args.workload == "cfg2" else None
+    except (OSError, ValueError, KeyError):
+        pass
     sm_mhz = r["clocks"].get("sm_mhz") or peaks["sm_max_mhz"]
     if top in fl:
         peak = 148 * 128 * 2 * peaks["sm_max_mhz"] * 1e6 / 1e12
         roof = {"kernel": top, "bound": "fp32", "achieved": stages[top]["tflops"], "peak": peak, "unit": "TFLOP/s",
-                "frac": stages[top]["tflops"] / peak, "traffic": None,
+                "frac": stages[top]["tflops"] / peak, "traffic": traffic,
                 "peak_source": "148 SM x 128 lanes x 2 x %.0f MHz (clocks.max.sm); no measured fp32 figure in "
                                "MEASURED_PEAKS.json" % peaks["sm_max_mhz"],
                 "frac_at_observed_clock": stages[top]["tflops"] / (148 * 128 * 2 * sm_mhz * 1e6 / 1e12),
                 "hbm_gbs": stages[top]["gbs"], "hbm_frac": stages[top]["hbm_frac"]}
     else:
         roof = {"kernel": top, "bound": "hbm", "achieved": stages[top]["gbs"], "peak": peaks["hbm_gbs"], "unit": "GB/s",
-                "frac": stages[top]["hbm_frac"], "traffic": None, "peak_source": peaks["source"]}
+                "frac": stages[top]["hbm_frac"], "traffic": traffic, "peak_source": peaks["source"]}
     value = world * args.steps / (r["ms_total"] * 1e-3)
     line = dict(base, impl="ours", value=value, ms_per_step=r["ms_total"] / args.steps, clocks=r["clocks"],
                 gpu_launches=r["launches"], roofline=roof, stages=stages,
