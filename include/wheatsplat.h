@@ -168,6 +168,29 @@ int ws_l1_ssim_backward(int32_t planes, int32_t height, int32_t width, const flo
                         const float *coef, int32_t per_plane, const void *scratch, size_t scratch_bytes,
                         float *dL_dimg, ws_stream_t stream);
 
+/* Optimiser step and densification bookkeeping either side of the backward.
+ * ws_adam_step = torch.optim.Adam(...).step() as GaussianModel.training_setup configures it
+ * (scene/gaussian_model.py:167-186; called at train_vanilla_3dgs.py:110-112): betas/eps shared, one
+ * learning rate and step count per parameter group, no weight decay, no amsgrad.  All groups (at most 8)
+ * are updated by ONE kernel launch, in place.  Tensors are contiguous float, 16-byte aligned. */
+typedef struct ws_adam_group {
+    float *param;        /* [numel] updated in place */
+    const float *grad;   /* [numel] */
+    float *exp_avg;      /* [numel] optimizer.state[p]["exp_avg"] */
+    float *exp_avg_sq;   /* [numel] optimizer.state[p]["exp_avg_sq"] */
+    int64_t numel;
+    double lr;           /* param_group["lr"] */
+    int64_t step;        /* state["step"] AFTER the increment of this call (>= 1) */
+} ws_adam_group;
+int ws_adam_step(int32_t n_groups, const ws_adam_group *groups, double beta1, double beta2, double eps,
+                 ws_stream_t stream);
+/* train_vanilla_3dgs.py:100-103 + GaussianModel.add_densification_stats (scene/gaussian_model.py:462-464):
+ * for every Gaussian with radii > 0: max_radii2D = max(max_radii2D, radii),
+ * xyz_gradient_accum += |dL_dmeans2D[:, :2]|, denom += 1.  radii int32[P], dL_dmeans2D float[P,3],
+ * the three accumulators float[P]. */
+int ws_densify_stats(int32_t P, const int32_t *radii, const float *dL_dmeans2D, float *max_radii2D,
+                     float *xyz_gradient_accum, float *denom, ws_stream_t stream);
+
 /* The stable LSD radix sort the rasterizer uses (replaces cub::DeviceRadixSort::SortPairs,
  * rasterizer_impl.cu:304-309), exposed for parity tests: sorts (u64 key, u32 value) pairs on
  * key bits [0, end_bit).  Results land in keys_out / vals_out; *_in are clobbered. */

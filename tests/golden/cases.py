@@ -118,3 +118,33 @@ def input_hash(arrays):
     for a in arrays:
         h.update(np.ascontiguousarray(a).tobytes())
     return h.hexdigest()
+
+
+# ---- optimiser step + densification statistics
+# group name: (shape per Gaussian, learning rate) -- scene/gaussian_model.py:172-179 with arguments/__init__.py defaults
+OPTIM_P = 257
+OPTIM_GROUPS = [
+    ("xyz", (3,), 0.00016 * 1.3),       # position_lr_init * spatial_lr_scale (rescheduled every step)
+    ("f_dc", (1, 3), 0.0025),
+    ("f_rest", (15, 3), 0.0025 / 20.0),
+    ("opacity", (1,), 0.05),
+    ("scaling", (3,), 0.005),
+    ("rotation", (4,), 0.001),
+]
+OPTIM_STEPS = 3
+OPTIM_XYZ_LRS = [0.00016 * 1.3, 0.00016 * 1.3 * 0.97, 0.00016 * 1.3 * 0.94]  # update_learning_rate() per iteration
+
+
+def optim_inputs(P=OPTIM_P, seed=11):
+    """Parameters, per-step gradients (rows of invisible Gaussians are zero, as the rasterizer backward leaves
+    them), radii and screen-space gradients for the densification statistics."""
+    rng = np.random.default_rng(seed)
+    params = {n: rng.normal(0, 1, (P,) + s).astype(np.float32) for n, s, _ in OPTIM_GROUPS}
+    grads, radii, g2d = [], [], []
+    for _ in range(OPTIM_STEPS):
+        vis = rng.random(P) < 0.7
+        grads.append({n: (rng.normal(0, 1, (P,) + s) * 10.0 ** rng.uniform(-6, 0, (P,) + (1,) * len(s))
+                          * vis.reshape((P,) + (1,) * len(s))).astype(np.float32) for n, s, _ in OPTIM_GROUPS})
+        radii.append((rng.integers(1, 60, P) * vis).astype(np.int32))
+        g2d.append((rng.normal(0, 1e-4, (P, 3)) * vis[:, None]).astype(np.float32))
+    return params, grads, radii, g2d

@@ -127,3 +127,33 @@ def test_loss_oracle_matches_reference_python(golden_dir, name):
     if "ssim_per_image" in gold.files:
         per = o["ssim_per_plane"].reshape(img.shape[0], -1).mean(axis=1)
         assert np.abs(per - gold["ssim_per_image"]).max() <= 1e-5
+
+
+def _optim_close(name, a, b):
+    """Optimiser tier: float32, ~1 ulp per operation; exp_avg cancels (g - m), hence the absolute floor."""
+    a, b = np.asarray(a, np.float32).reshape(-1), np.asarray(b, np.float32).reshape(-1)
+    lim = 2e-6 * np.abs(b) + 2e-7 * np.abs(b).max()
+    bad = np.abs(a - b) > lim
+    assert not bad.any(), "%s: %d elements off, max err %g" % (name, bad.sum(), np.abs(a - b).max())
+
+
+def test_optim_oracle_matches_torch_adam_and_reference_stats(golden_dir):
+    """oracle/optim_oracle.py against torch.optim.Adam as GaussianModel.training_setup configures it and the
+    reference's own add_densification_stats (tests/golden/make_golden_optim.py)."""
+    import optim_oracle
+    gold = _load(golden_dir, "optim")
+    params, grads, radii, g2d = cases.optim_inputs()
+    assert str(gold["input_sha256"]) == cases.input_hash([params[n] for n, _, _ in cases.OPTIM_GROUPS])
+    P = cases.OPTIM_P
+    st = {n: (params[n], np.zeros_like(params[n]), np.zeros_like(params[n])) for n, _, _ in cases.OPTIM_GROUPS}
+    mr, acc, dn = (np.zeros(P, np.float32) for _ in range(3))
+    for it in range(cases.OPTIM_STEPS):
+        mr, acc, dn = optim_oracle.densify_stats(radii[it], g2d[it], mr, acc, dn)
+        assert np.array_equal(mr, gold["step%d_max_radii2D" % it])
+        assert np.array_equal(dn, gold["step%d_denom" % it].reshape(-1))
+        _optim_close("xyz_gradient_accum", acc, gold["step%d_xyz_gradient_accum" % it])
+        for n, _, lr in cases.OPTIM_GROUPS:
+            lr = cases.OPTIM_XYZ_LRS[it] if n == "xyz" else lr
+            st[n] = optim_oracle.adam_step(st[n][0], grads[it][n], st[n][1], st[n][2], it + 1, lr)
+            for suffix, a in zip(("", "_exp_avg", "_exp_avg_sq"), st[n]):
+                _optim_close("step %d %s%s" % (it, n, suffix), a, gold["step%d_%s%s" % (it, n, suffix)])

@@ -18,6 +18,7 @@ SYMBOLS = [
     "ws_forward_prepare", "ws_forward_render", "ws_backward", "ws_mark_visible", "ws_knn_bytes",
     "ws_knn_dist2", "ws_multi_instance_opt", "ws_sort_bytes", "ws_sort_pairs_u64", "ws_sort_pairs_u32", "ws_set_binning_mode",
     "ws_loss_bytes", "ws_l1_ssim_forward", "ws_l1_ssim_backward", "ws_debug_fetch",
+    "ws_adam_step", "ws_densify_stats",
     "ws_launch_count", "ws_prof_enable", "ws_prof_read", "ws_prof_stage_name", "ws_debug_count_pairs",
 ]
 WS_PROF_NSTAGES = 8
@@ -46,6 +47,11 @@ class WsGrads(C.Structure):
     _fields_ = [("dL_dmeans2D", C.c_void_p), ("dL_dcolors", C.c_void_p), ("dL_dopacity", C.c_void_p),
                 ("dL_dmeans3D", C.c_void_p), ("dL_dcov3D", C.c_void_p), ("dL_dsh", C.c_void_p),
                 ("dL_dscales", C.c_void_p), ("dL_drotations", C.c_void_p)]
+
+
+class WsAdamGroup(C.Structure):
+    _fields_ = [("param", C.c_void_p), ("grad", C.c_void_p), ("exp_avg", C.c_void_p), ("exp_avg_sq", C.c_void_p),
+                ("numel", C.c_int64), ("lr", C.c_double), ("step", C.c_int64)]
 
 
 _lib = None
@@ -106,6 +112,10 @@ def load():
     lib.ws_l1_ssim_forward.argtypes = [i32, i32, i32, vp, vp, vp, vp, sz, vp]
     lib.ws_l1_ssim_backward.restype = C.c_int
     lib.ws_l1_ssim_backward.argtypes = [i32, i32, i32, vp, vp, vp, i32, vp, sz, vp, vp]
+    lib.ws_adam_step.restype = C.c_int
+    lib.ws_adam_step.argtypes = [i32, C.POINTER(WsAdamGroup), C.c_double, C.c_double, C.c_double, vp]
+    lib.ws_densify_stats.restype = C.c_int
+    lib.ws_densify_stats.argtypes = [i32, vp, vp, vp, vp, vp, vp]
     lib.ws_set_binning_mode.restype = C.c_int
     lib.ws_set_binning_mode.argtypes = [i32]
     lib.ws_sort_pairs_u32.restype = C.c_int
