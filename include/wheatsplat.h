@@ -168,6 +168,33 @@ int ws_l1_ssim_backward(int32_t planes, int32_t height, int32_t width, const flo
                         const float *coef, int32_t per_plane, const void *scratch, size_t scratch_bytes,
                         float *dL_dimg, ws_stream_t stream);
 
+/* Batched eval_obj_labels (replaces utils/wheatgs_helper.py:245-271 = eval_wheatgs.py:29-64):
+ * the segmentation image of one view from the per-object Gaussian sets, with ONE preprocess, ONE binning pass
+ * keyed by (object, tile), ONE blend launch and ONE merge kernel instead of one flashsplat_render + two
+ * image copies to the CPU per object.  Object sets are CSR lists by Gaussian: Gaussian g belongs to the objects
+ * member_obj[member_start[g] .. member_start[g+1]) (ascending, each in 1..num_rows-1; row 0 = background is
+ * never rendered, wheatgs_helper.py:254).  Three calls, split at the two counts the caller sizes memory by:
+ *   ws_objeval_prepare -> number of (object, tile, Gaussian) instances R'  (geom as ws_forward_prepare)
+ *   ws_objeval_bin     -> number of non-empty (object, tile) jobs J         (binning: ws_binning_bytes(R');
+ *                                                                            scratch: ws_objeval_bytes(...))
+ *   ws_objeval_render  -> pred_mask float[H*W]: object id per pixel, 0 = none (job_out: J*256*2 floats)
+ * Per-object alpha and depth are bit-identical to the subset renders; the front/behind decision compares the
+ * two means accumulated in double and rounded to float. */
+typedef struct ws_objsets {
+    int32_t num_rows;             /* rows of all_obj_labels (objects 1..num_rows-1) */
+    const int32_t *member_start;  /* device int32[P+1] */
+    const int32_t *member_obj;    /* device int32[member_start[P]] */
+} ws_objsets;
+size_t ws_objeval_bytes(int32_t num_rows, int32_t width, int32_t height, int64_t num_instances);
+int64_t ws_objeval_prepare(const ws_view *view, const ws_gaussians *g, const ws_objsets *sets, int32_t *radii,
+                           void *geom, size_t geom_bytes, ws_stream_t stream);
+int64_t ws_objeval_bin(const ws_view *view, const ws_gaussians *g, const ws_objsets *sets, const int32_t *radii,
+                       void *geom, void *binning, size_t binning_bytes, void *scratch, size_t scratch_bytes,
+                       int64_t num_instances, ws_stream_t stream);
+int ws_objeval_render(const ws_view *view, const ws_objsets *sets, void *binning, void *scratch,
+                      size_t scratch_bytes, int64_t num_instances, int64_t num_jobs, float *job_out,
+                      size_t job_out_bytes, float *pred_mask, ws_stream_t stream);
+
 /* Optimiser step and densification bookkeeping either side of the backward.
  * ws_adam_step = torch.optim.Adam(...).step() as GaussianModel.training_setup configures it
  * (scene/gaussian_model.py:167-186; called at train_vanilla_3dgs.py:110-112): betas/eps shared, one

@@ -148,3 +148,27 @@ def optim_inputs(P=OPTIM_P, seed=11):
         radii.append((rng.integers(1, 60, P) * vis).astype(np.int32))
         g2d.append((rng.normal(0, 1e-4, (P, 3)) * vis[:, None]).astype(np.float32))
     return params, grads, radii, g2d
+
+
+# ---- batched eval_obj_labels
+OBJEVAL = dict(P=4000, W=200, H=150, cam=17, n_heads=8, extent=(0.3, 0.2, 0.12))
+
+
+def objeval_inputs():
+    """A small dense scene (8 heads in a 30 x 20 cm plot seen from above) and an all_obj_labels matrix that
+    exercises every branch of eval_obj_labels: plain heads, an object IN FRONT of an earlier one (the upper half of
+    head 0: it repaints), an object BEHIND earlier ones (head 1, the lower half of head 0 and the so far
+    unpainted head 7: it only takes free pixels), a Gaussian in several objects, an empty row, and row 0 (background, never rendered)."""
+    c = OBJEVAL
+    sc = scene.synthetic_scene(c["P"], seed=3, n_heads=c["n_heads"], scale_median=0.004, extent=c["extent"])
+    cam = scene.overhead_cameras(c["W"], c["H"], extent=c["extent"])[c["cam"]]
+    hid, z = sc["head_id"], sc["means3D"][:, 2]
+    zc = sc["head_centers"][:, 2]
+    rows = [hid < 0]                                        # 0: background
+    rows += [hid == k for k in range(c["n_heads"] - 1)]     # 1..7: heads 0..6
+    rows.append((hid == 0) & (z > zc[0]))                   # 8: upper half of head 0 (in front of object 1)
+    rows.append((hid == 1) | ((hid == 0) & (z <= zc[0])) | (hid == 7))  # 9: behind objects 2 and 8 where it overlaps
+    #                                                         them; head 7 is free, so it is painted there only
+    rows.append(np.zeros_like(hid, dtype=bool))             # 10: empty
+    rows.append((hid == 2) | (hid == 3))                    # 11: two heads at once
+    return sc, cam, np.stack(rows).astype(bool)

@@ -157,3 +157,22 @@ def test_optim_oracle_matches_torch_adam_and_reference_stats(golden_dir):
             st[n] = optim_oracle.adam_step(st[n][0], grads[it][n], st[n][1], st[n][2], it + 1, lr)
             for suffix, a in zip(("", "_exp_avg", "_exp_avg_sq"), st[n]):
                 _optim_close("step %d %s%s" % (it, n, suffix), a, gold["step%d_%s%s" % (it, n, suffix)])
+
+
+def test_segment_oracle_matches_reference_eval_obj_labels(golden_dir):
+    """oracle/segment_oracle.py against the reference: per-object alpha/depth from the unmodified reference
+    flashsplat rasterizer (B200) and the pred_mask its own eval_obj_labels paints from them."""
+    import segment_oracle
+    gold = _load(golden_dir, "objeval")
+    sc, cam, labels = cases.objeval_inputs()
+    keys = ("means3D", "opacities", "scales", "rotations", "shs")
+    assert str(gold["input_sha256"]) == cases.input_hash([sc[k] for k in keys] + [labels.astype(np.uint8)])
+    pred, renders = segment_oracle.eval_obj_labels(labels, sc, cam, cases.BG, sh_degree=3, return_renders=True)
+    assert sorted(renders) == gold["rendered_rows"].tolist()
+    for i, (alpha, depth) in renders.items():
+        assert np.abs(alpha - gold["alpha_%d" % i]).max() <= 1e-4
+        assert np.abs(depth - gold["depth_%d" % i]).max() <= 1e-4
+    assert np.array_equal(pred, gold["pred_mask"])
+    # the merge alone, fed the reference's own renders
+    again = segment_oracle.merge({i: (gold["alpha_%d" % i], gold["depth_%d" % i]) for i in renders}, pred.shape)
+    assert np.array_equal(again, gold["pred_mask"])

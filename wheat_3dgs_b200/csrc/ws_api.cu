@@ -68,7 +68,7 @@ struct ProfScope {
     }
 };
 
-static cudaEvent_t total_event()
+cudaEvent_t total_event()
 {
     static thread_local cudaEvent_t ev[16] = {};
     int dev = 0;
@@ -80,7 +80,7 @@ static cudaEvent_t total_event()
 
 // pinned landing word for num_rendered: a D2H copy into pageable memory blocks the host until
 // the stream has drained, a copy into pinned memory is asynchronous
-static uint32_t *total_host()
+uint32_t *total_host()
 {
     static thread_local uint32_t *p = nullptr;
     if (!p && cudaHostAlloc((void **)&p, 64, cudaHostAllocDefault) != cudaSuccess) p = nullptr;
@@ -88,7 +88,7 @@ static uint32_t *total_host()
 }
 
 // DGR rasterizer_impl.cu:35-50
-static uint32_t get_higher_msb(uint32_t n)
+uint32_t get_higher_msb(uint32_t n)
 {
     uint32_t msb = sizeof(n) * 4, step = msb;
     while (step > 1) {
@@ -99,7 +99,7 @@ static uint32_t get_higher_msb(uint32_t n)
     return msb;
 }
 
-static int check_view_gauss(const char *who, const ws_view *v, const ws_gaussians *g, bool need_opacity = true)
+int check_view_gauss(const char *who, const ws_view *v, const ws_gaussians *g, bool need_opacity)
 {
     if (!v || !g) { set_error("%s: NULL view/gaussians", who); return WS_E_INVALID; }
     if (g->P <= 0) { set_error("%s: P must be > 0 (the wrapper handles empty inputs)", who); return WS_E_INVALID; }

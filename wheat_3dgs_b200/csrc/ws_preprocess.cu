@@ -354,6 +354,13 @@ __global__ void __launch_bounds__(1024) scan_block_sums(int nb, const uint32_t *
     if (tid == 0) total[0] = s_carry;
 }
 
+int launch_scan_u32(int nb, const uint32_t *sums, uint32_t *offsets, uint32_t *total, cudaStream_t st, bool debug)
+{
+    scan_block_sums<<<1, 1024, 0, st>>>(nb, sums, offsets, total);
+    WS_LAUNCH_CHECK(st, debug);
+    return WS_OK;
+}
+
 int launch_scan_blocks(int P, GeomState &gs, cudaStream_t st, bool debug)
 {
     const int nb = (P + WS_PRE_THREADS - 1) / WS_PRE_THREADS;

@@ -59,11 +59,19 @@ struct RenderFwdParams {
     float *used_count;
     int32_t *out_contrib_num;
     int num_obj;
+    // (object, tile) jobs of the batched eval_obj_labels (ws_objeval.cu): CTA group j blends the records of
+    // ranges[jobs[j]] over tile jobs[j] % tiles_total and writes alpha/depth of its 256 pixels to job_*[j][16][16]
+    const uint32_t *jobs;
+    int tiles_total;
+    float *job_alpha, *job_depth;
 };
 
-template <bool FLASH>
+// MODE 0: the DGR rasterizer; 1: flashsplat (label votes); 2: (object, tile) jobs, alpha and depth only
+template <int MODE>
 __global__ void __launch_bounds__(RF_THREADS) render_fwd(const RenderFwdParams p)
 {
+    constexpr bool FLASH = MODE == 1;
+    constexpr bool JOBS = MODE == 2;
     __shared__ __align__(128) float4 s_q0[2][RF_BATCH];
     __shared__ __align__(128) float4 s_q1[2][RF_BATCH];
     __shared__ __align__(128) float4 s_q2[2][RF_BATCH];
@@ -72,7 +80,9 @@ __global__ void __launch_bounds__(RF_THREADS) render_fwd(const RenderFwdParams p
     const int lane = threadIdx.x & 31;
     const bool leader = threadIdx.x == 0;
     // the CTAs of a tile are adjacent in launch order
-    const uint32_t tile = blockIdx.x / (4 / RF_WARPS);
+    const uint32_t slot0 = blockIdx.x / (4 / RF_WARPS);
+    const uint32_t slot = JOBS ? __ldg(p.jobs + slot0) : slot0;           // index into ranges
+    const uint32_t tile = JOBS ? slot % (uint32_t)p.tiles_total : slot;
     const uint32_t w = (blockIdx.x % (4 / RF_WARPS)) * RF_WARPS + (threadIdx.x >> 5);
     const int tile_y = (int)(tile / (uint32_t)p.tiles_x), tile_x = (int)(tile - (uint32_t)tile_y * p.tiles_x);
     const int wx0 = tile_x * WS_BLOCK_X + (int)(w & 1) * 8;
@@ -84,7 +94,7 @@ __global__ void __launch_bounds__(RF_THREADS) render_fwd(const RenderFwdParams p
     const f2 npy = pk2(-(float)py0, -(float)py1);
     const float fx0 = (float)wx0, fy0 = (float)wy0;
 
-    const uint2 range = p.ranges[tile];
+    const uint2 range = p.ranges[slot];
     const int n = (int)(range.y - range.x);
     const int nb = (n + RF_BATCH - 1) / RF_BATCH;
 
@@ -223,6 +233,17 @@ __global__ void __launch_bounds__(RF_THREADS) render_fwd(const RenderFwdParams p
         }
     }
 
+    if (JOBS) {
+        // every slot of the job's 16x16 block is written (zeros outside the image)
+        const uint32_t li = (uint32_t)(py0 - tile_y * WS_BLOCK_Y) * WS_BLOCK_X + (uint32_t)(px - tile_x * WS_BLOCK_X);
+        float *ja = p.job_alpha + (size_t)slot0 * (WS_BLOCK_X * WS_BLOCK_Y);
+        float *jd = p.job_depth + (size_t)slot0 * (WS_BLOCK_X * WS_BLOCK_Y);
+        ja[li] = in0 ? Wa : 0.0f;
+        jd[li] = in0 ? Da : 0.0f;
+        ja[li + 4 * WS_BLOCK_X] = in1 ? Wb : 0.0f;
+        jd[li + 4 * WS_BLOCK_X] = in1 ? Db : 0.0f;
+        return;
+    }
     const size_t HW = (size_t)p.H * p.W;
     const float bg0 = __ldg(p.bg + 0), bg1 = __ldg(p.bg + 1), bg2 = __ldg(p.bg + 2);
     // forward.cu:376-377: C + T * bg (contracted to one FMA in the reference build)
@@ -267,10 +288,29 @@ int launch_render_fwd(const ws_view *v, int P, GeomState &gs, BinningState &bs, 
     p.num_obj = fl ? fl->num_obj : 0;
     p.tiles_x = (p.W + WS_BLOCK_X - 1) / WS_BLOCK_X;
     const unsigned grid = (unsigned)(4 / RF_WARPS) * (unsigned)p.tiles_x * (unsigned)((p.H + WS_BLOCK_Y - 1) / WS_BLOCK_Y);
+    p.jobs = nullptr; p.tiles_total = 0; p.job_alpha = nullptr; p.job_depth = nullptr;
     if (fl)
-        render_fwd<true><<<grid, RF_THREADS, 0, st>>>(p);
+        render_fwd<1><<<grid, RF_THREADS, 0, st>>>(p);
     else
-        render_fwd<false><<<grid, RF_THREADS, 0, st>>>(p);
+        render_fwd<0><<<grid, RF_THREADS, 0, st>>>(p);
+    WS_LAUNCH_CHECK(st, v->debug);
+    return WS_OK;
+}
+
+int launch_render_jobs(const ws_view *v, const uint2 *ranges, const uint32_t *jobs, int n_jobs, int T,
+                       BinningState &bs, float *job_alpha, float *job_depth, cudaStream_t st)
+{
+    if (n_jobs <= 0) return WS_OK;
+    RenderFwdParams p;
+    p.ranges = ranges; p.q0 = bs.q0; p.q1 = bs.q1; p.q2 = bs.q2;
+    p.W = v->image_width; p.H = v->image_height; p.P = 0;
+    p.bg = v->bg;
+    p.out_color = nullptr; p.out_depth = nullptr; p.out_alpha = nullptr; p.n_contrib = nullptr;
+    p.gt_mask = nullptr; p.unique_label = nullptr; p.used_count = nullptr; p.out_contrib_num = nullptr;
+    p.num_obj = 0;
+    p.tiles_x = (p.W + WS_BLOCK_X - 1) / WS_BLOCK_X;
+    p.jobs = jobs; p.tiles_total = T; p.job_alpha = job_alpha; p.job_depth = job_depth;
+    render_fwd<2><<<(unsigned)(4 / RF_WARPS) * (unsigned)n_jobs, RF_THREADS, 0, st>>>(p);
     WS_LAUNCH_CHECK(st, v->debug);
     return WS_OK;
 }

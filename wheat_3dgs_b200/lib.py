@@ -19,6 +19,7 @@ SYMBOLS = [
     "ws_knn_dist2", "ws_multi_instance_opt", "ws_sort_bytes", "ws_sort_pairs_u64", "ws_sort_pairs_u32", "ws_set_binning_mode",
     "ws_loss_bytes", "ws_l1_ssim_forward", "ws_l1_ssim_backward", "ws_debug_fetch",
     "ws_adam_step", "ws_densify_stats",
+    "ws_objeval_bytes", "ws_objeval_prepare", "ws_objeval_bin", "ws_objeval_render",
     "ws_launch_count", "ws_prof_enable", "ws_prof_read", "ws_prof_stage_name", "ws_debug_count_pairs",
 ]
 WS_PROF_NSTAGES = 8
@@ -47,6 +48,10 @@ class WsGrads(C.Structure):
     _fields_ = [("dL_dmeans2D", C.c_void_p), ("dL_dcolors", C.c_void_p), ("dL_dopacity", C.c_void_p),
                 ("dL_dmeans3D", C.c_void_p), ("dL_dcov3D", C.c_void_p), ("dL_dsh", C.c_void_p),
                 ("dL_dscales", C.c_void_p), ("dL_drotations", C.c_void_p)]
+
+
+class WsObjSets(C.Structure):
+    _fields_ = [("num_rows", C.c_int32), ("member_start", C.c_void_p), ("member_obj", C.c_void_p)]
 
 
 class WsAdamGroup(C.Structure):
@@ -112,6 +117,15 @@ def load():
     lib.ws_l1_ssim_forward.argtypes = [i32, i32, i32, vp, vp, vp, vp, sz, vp]
     lib.ws_l1_ssim_backward.restype = C.c_int
     lib.ws_l1_ssim_backward.argtypes = [i32, i32, i32, vp, vp, vp, i32, vp, sz, vp, vp]
+    lib.ws_objeval_bytes.restype = sz
+    lib.ws_objeval_bytes.argtypes = [i32, i32, i32, i64]
+    lib.ws_objeval_prepare.restype = i64
+    lib.ws_objeval_prepare.argtypes = [C.POINTER(WsView), C.POINTER(WsGaussians), C.POINTER(WsObjSets), vp, vp, sz, vp]
+    lib.ws_objeval_bin.restype = i64
+    lib.ws_objeval_bin.argtypes = [C.POINTER(WsView), C.POINTER(WsGaussians), C.POINTER(WsObjSets), vp, vp, vp, sz,
+                                   vp, sz, i64, vp]
+    lib.ws_objeval_render.restype = C.c_int
+    lib.ws_objeval_render.argtypes = [C.POINTER(WsView), C.POINTER(WsObjSets), vp, vp, sz, i64, i64, vp, sz, vp, vp]
     lib.ws_adam_step.restype = C.c_int
     lib.ws_adam_step.argtypes = [i32, C.POINTER(WsAdamGroup), C.c_double, C.c_double, C.c_double, vp]
     lib.ws_densify_stats.restype = C.c_int
