@@ -224,7 +224,9 @@ def run_ours(args, rank, world, local):
     lg = scene.loss_gradients((3, H, W), seed=2)
     dc, dd, da = [torch.from_numpy(lg[k]).to(dev) for k in ("dL_dcolor", "dL_ddepth", "dL_dalpha")]
     e = torch.Tensor([])
-    bucket = torch.empty((wdist.full_bucket_numel(P, M),), dtype=torch.float32, device=dev)
+    # gradient bucket: symmetric memory + libwheatsplat's own all-reduce kernel when N > 1 (NCCL if unavailable)
+    bucket, reduce_bucket, reduce_how = wdist.make_bucket(wdist.full_bucket_numel(P, M), dev)
+    n_train = wdist.train_bucket_numel(P, M)
 
     def view_of(i):
         return (rank + i * world) % nv
@@ -246,7 +248,7 @@ def run_ours(args, rank, world, local):
         fw = fwd(c)
         bwd(c, fw)
         if reduce and world > 1:
-            wdist.allreduce_train_grads(bucket, P, M)
+            reduce_bucket(n_train)
         return fw
 
     def barrier():
@@ -306,7 +308,7 @@ def run_ours(args, rank, world, local):
         loss.backward()
         pre.release(sl)
         if world > 1:
-            wdist.allreduce_train_grads(bucket, P, M)
+            reduce_bucket(n_train)
         val = loss.item()  # device -> host read of the step's result
         for p_ in list(params.values()) + [means2D]:
             p_.grad = None
@@ -343,6 +345,7 @@ def run_ours(args, rank, world, local):
     for k in stats:
         stats[k] /= float(nprof)
     return dict(P=P, W=W, H=H, nv=nv, M=M, ms_total=ms_total, ms_e2e=ms_e2e, launches=launches, clocks=clocks,
+                reduce_how=reduce_how,
                 prof=prof, nprof=nprof, stats=stats, h2d=h2d, d2h=4)
 
 
@@ -547,6 +550,8 @@ def main():
                 work_per_view={k: st[k] for k in ("V", "R", "n_eval", "n_contrib")},
                 e2e={"value": world * args.steps / (r["ms_e2e"] * 1e-3), "unit": "views/s",
                      "h2d_bytes_per_step": r["h2d"], "d2h_bytes_per_step": r["d2h"]})
+    if world > 1:
+        line["config"] = dict(config, all_reduce=r["reduce_how"])
     if world == 1 and not args.no_cpu_baseline:
         cv, cores, sample = run_cpu_oracle(args.workload)
         line["cpu_baseline"] = {"value": cv, "unit": "views/s", "cores": cores, "kind": "port", "sample": sample}

@@ -48,7 +48,7 @@ typedef struct CUstream_st *ws_stream_t;
 #define WS_E_CUDA (-3)      /* a CUDA runtime call or kernel launch failed */
 #define WS_E_UNSUPPORTED (-4)
 
-#define WS_ABI_VERSION 1
+#define WS_ABI_VERSION 2
 
 /* Per-view constants = GaussianRasterizationSettings
  * (DGR/diff_gaussian_rasterization/__init__.py:160-172; FSR adds mask_grad, num_obj:
@@ -79,6 +79,12 @@ typedef struct ws_gaussians {
     const float *scales;         /* [P,3] post-exp, or NULL */
     const float *rotations;      /* [P,4] (w,x,y,z), NOT normalised in-kernel (forward.cu:127), or NULL */
     const float *cov3D_precomp;  /* [P,6] or NULL; exactly one of (scales,rotations) / cov3D_precomp */
+    /* GaussianModel's getters folded into the kernels (scene/gaussian_model.py:101-121): */
+    const float *shs_rest;       /* NULL, or features_rest [P,M-1,3]: then shs is features_dc [P,1,3] and the
+                                    torch.cat of get_features (:113-116) is never materialised */
+    int32_t raw_params;          /* != 0: opacities are logits (sigmoid in-kernel, :109-110), scales are
+                                    log-scales (exp, :101-102), rotations unnormalised (normalize, :105-106);
+                                    the backward returns gradients w.r.t. these raw tensors */
 } ws_gaussians;
 
 /* flashsplat additions (FSR/rasterize_points.cu:36-131).  Pass NULL for the plain DGR op. */
@@ -106,6 +112,7 @@ typedef struct ws_grads {
     float *dL_dsh;        /* [P,M,3] or NULL when M == 0 */
     float *dL_dscales;    /* [P,3] */
     float *dL_drotations; /* [P,4] */
+    float *dL_dsh_rest;   /* [P,M-1,3] when ws_gaussians.shs_rest is given (dL_dsh is then [P,1,3]), else NULL */
 } ws_grads;
 
 int ws_abi_version(void);
@@ -217,6 +224,15 @@ int ws_adam_step(int32_t n_groups, const ws_adam_group *groups, double beta1, do
  * the three accumulators float[P]. */
 int ws_densify_stats(int32_t P, const int32_t *radii, const float *dL_dmeans2D, float *max_radii2D,
                      float *xyz_gradient_accum, float *denom, ws_stream_t stream);
+
+/* Exchange step of data-parallel training: in-place SUM over ranks of a float buffer that lives in
+ * symmetric memory (every rank has mapped every peer's copy), by one kernel on the caller's stream.  Rank r
+ * reduces the r-th slice: with multicast_ptr != NULL (NVSwitch multicast address aliasing all copies) through
+ * multimem.ld_reduce / multimem.st, else with loads from / stores to peer_ptrs[0..world) in rank order.  All
+ * ranks call it with the same numel (a multiple of 4), after a barrier that orders every rank's writes to the
+ * buffer before it, and follow it with a barrier before reading the sums.  num_ctas <= 0: one CTA per SM. */
+int ws_allreduce_sum_f32(int32_t rank, int32_t world, int64_t numel, void *multicast_ptr, void *const *peer_ptrs,
+                         int32_t num_ctas, ws_stream_t stream);
 
 /* The stable LSD radix sort the rasterizer uses (replaces cub::DeviceRadixSort::SortPairs,
  * rasterizer_impl.cu:304-309), exposed for parity tests: sorts (u64 key, u32 value) pairs on

@@ -42,6 +42,8 @@ struct PreParams {
     uint8_t *clamped;
     float *image_xys, *gs_depth; // flashsplat extras or NULL
     int sh_vec4;                 // 1: 3M % 4 == 0 and shs 16-byte aligned -> float4 staging
+    const float *shs_rest;       // features_rest [P,M-1,3] (shs is then features_dc [P,1,3]) or NULL
+    int raw;                     // opacities/scales/rotations are GaussianModel's raw parameters
 };
 
 // DGR forward.cu:118-152; op order from the reference SASS (see oracle/splat_oracle.c).
@@ -168,6 +170,21 @@ __global__ void __launch_bounds__(WS_PRE_THREADS) preprocess_fwd(const PreParams
                 int g = i / row4, c = i - g * row4;
                 s_sh4[g * srow4 + c] = __ldg(src + i);
             }
+        } else if (p.shs_rest) {
+            // features_dc and features_rest staged side by side into the rows torch.cat would have built
+            float *s_sh = reinterpret_cast<float *>(s_sh4);
+            const int srow = row_f | 1, rest_f = row_f - 3;
+            const float *src = p.shs + (size_t)base * 3;
+            for (int i = tid; i < nvalid * 3; i += WS_PRE_THREADS) {
+                int g = i / 3, c = i - g * 3;
+                s_sh[g * srow + c] = __ldg(src + i);
+            }
+            src = p.shs_rest + (size_t)base * rest_f;
+            const int n = nvalid * rest_f;
+            for (int i = tid; i < n; i += WS_PRE_THREADS) {
+                int g = i / rest_f, c = i - g * rest_f;
+                s_sh[g * srow + 3 + c] = __ldg(src + i);
+            }
         } else {
             float *s_sh = reinterpret_cast<float *>(s_sh4);
             const int srow = row_f | 1; // odd stride -> conflict-free
@@ -200,9 +217,10 @@ __global__ void __launch_bounds__(WS_PRE_THREADS) preprocess_fwd(const PreParams
 #pragma unroll
                 for (int k = 0; k < 6; k++) c3[k] = p.cov3D_precomp[6 * (size_t)idx + k];
             } else {
-                const float4 q = reinterpret_cast<const float4 *>(p.rotations)[idx];
-                const float s0 = p.scales[3 * (size_t)idx], s1 = p.scales[3 * (size_t)idx + 1],
-                            s2 = p.scales[3 * (size_t)idx + 2];
+                float4 q = reinterpret_cast<const float4 *>(p.rotations)[idx];
+                float s0 = p.scales[3 * (size_t)idx], s1 = p.scales[3 * (size_t)idx + 1],
+                      s2 = p.scales[3 * (size_t)idx + 2];
+                if (p.raw) raw_activate(q, s0, s1, s2);
                 compute_cov3d(__fmul_rn(s0, p.scale_modifier), __fmul_rn(s1, p.scale_modifier),
                               __fmul_rn(s2, p.scale_modifier), q.x, q.y, q.z, q.w, c3);
             }
@@ -246,7 +264,7 @@ __global__ void __launch_bounds__(WS_PRE_THREADS) preprocess_fwd(const PreParams
                         g = p.colors_precomp[3 * (size_t)idx + 1];
                         b = p.colors_precomp[3 * (size_t)idx + 2];
                     }
-                    const float opac = p.opacities[idx];
+                    const float opac = p.raw ? raw_sigmoid(p.opacities[idx]) : p.opacities[idx];
                     p.g0[idx] = make_float4(pix, piy, conx, cony);
                     p.g1[idx] = make_float4(conz, opac, pvz, logf(255.0f * opac));
                     p.g2[idx] = make_float4(r, g, b, 0.0f);
@@ -290,6 +308,7 @@ int launch_preprocess(const ws_view *v, const ws_gaussians *g, int32_t *radii, G
     p.means3D = g->means3D; p.shs = g->shs; p.colors_precomp = g->colors_precomp;
     p.opacities = g->opacities; p.scales = g->scales; p.rotations = g->rotations;
     p.cov3D_precomp = g->cov3D_precomp;
+    p.shs_rest = g->shs ? g->shs_rest : nullptr; p.raw = g->raw_params;
     p.view = v->viewmatrix; p.proj = v->projmatrix; p.campos = v->campos;
     p.radii = radii; p.g0 = gs.g0; p.g1 = gs.g1; p.g2 = gs.g2;
     p.tiles_touched = gs.tiles_touched; p.block_sums = gs.block_sums; p.clamped = gs.clamped;
@@ -297,7 +316,7 @@ int launch_preprocess(const ws_view *v, const ws_gaussians *g, int32_t *radii, G
     p.image_xys = fl ? fl->image_xys : nullptr;
     p.gs_depth = fl ? fl->gs_depth : nullptr;
     const int row_f = 3 * g->M;
-    p.sh_vec4 = (g->shs && row_f % 4 == 0 && ((uintptr_t)g->shs % 16) == 0) ? 1 : 0;
+    p.sh_vec4 = (g->shs && !p.shs_rest && row_f % 4 == 0 && ((uintptr_t)g->shs % 16) == 0) ? 1 : 0;
     size_t smem = 0;
     if (!g->colors_precomp)
         smem = p.sh_vec4 ? (size_t)WS_PRE_THREADS * (row_f / 4 + 1) * 16 : (size_t)WS_PRE_THREADS * (row_f | 1) * 4;

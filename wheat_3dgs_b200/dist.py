@@ -87,6 +87,68 @@ def allreduce_train_grads(bucket, P, M, async_op=False):
     return dist.all_reduce(bucket[:train_bucket_numel(P, M)], op=dist.ReduceOp.SUM, async_op=async_op)
 
 
+class SymmetricBucket:
+    """The gradient bucket in symmetric memory (every rank maps every peer's copy; with NVSwitch also one
+    multicast address for all of them), summed over ranks in place by ONE kernel of libwheatsplat
+    (csrc/ws_collective.cu: multimem.ld_reduce / multimem.st, or peer loads and stores) on the CURRENT stream,
+    bracketed by the symmetric-memory barrier -- no hand-off to NCCL's stream.  NCCL stays the plumbing
+    (rendezvous, everything else in this module) and the fallback of `make_bucket` when symmetric memory
+    cannot be set up.  `tensor` is what ops._backward() writes into."""
+
+    def __init__(self, numel, device, group=None):
+        import ctypes as C
+        import torch.distributed._symmetric_memory as symm
+        from . import lib as _lib
+        self._lib, self._C = _lib, C
+        group = group if group is not None else dist.group.WORLD
+        self.numel = (int(numel) + 3) // 4 * 4
+        self.tensor = symm.empty(self.numel, dtype=torch.float32, device=device)
+        self.hdl = symm.rendezvous(self.tensor, group.group_name)
+        self.rank, self.world = self.hdl.rank, self.hdl.world_size
+        # Link traffic per direction for a bucket of S bytes on W GPUs: multicast (1 + 1/W) S, peer loads/stores
+        # 2 (W-1)/W S -> multicast from W = 4 up (measured at W = 2: peers 0.39 ms, multicast 0.62 ms, NCCL 0.49 ms
+        # for 248 MB).  WS_ALLREDUCE_KERNEL=peers|multimem overrides.
+        self.multicast = int(self.hdl.multicast_ptr or 0)   # 0: no NVSwitch multicast
+        want = os.environ.get("WS_ALLREDUCE_KERNEL", "multimem" if self.world >= 4 else "peers")
+        if want == "peers" or os.environ.get("WS_ALLREDUCE_PEERS"):
+            self.multicast = 0
+        self.peers = (C.c_void_p * self.world)(*[int(p) for p in self.hdl.buffer_ptrs])
+        self.num_ctas = int(os.environ.get("WS_ALLREDUCE_CTAS", "0"))
+
+    def all_reduce_(self, numel=None):
+        """SUM over ranks of tensor[:numel] (default: all of it), in place, on the current stream."""
+        n = self.numel if numel is None else (int(numel) + 3) // 4 * 4
+        L = self._lib.load()
+        self.hdl.barrier(channel=0)
+        with torch.cuda.device(self.tensor.device):
+            st = self._C.c_void_p(torch.cuda.current_stream().cuda_stream)
+            self._lib.check(L.ws_allreduce_sum_f32(self.rank, self.world, n, self._C.c_void_p(self.multicast or None),
+                                                   self.peers, self.num_ctas, st), "ws_allreduce_sum_f32")
+        self.hdl.barrier(channel=1)
+        return self.tensor
+
+
+def make_bucket(numel, device):
+    """(tensor, reduce) for the gradient bucket: a SymmetricBucket summed by libwheatsplat's own kernel when the
+    group spans GPUs with peer access, else a plain tensor summed by one NCCL all_reduce.  WS_ALLREDUCE=nccl
+    forces the latter."""
+    if world_size() > 1 and torch.device(device).type == "cuda" and os.environ.get("WS_ALLREDUCE", "") != "nccl":
+        try:
+            sb = SymmetricBucket(numel, device)
+            return sb.tensor, sb.all_reduce_, "libwheatsplat multimem kernel" if sb.multicast else "libwheatsplat peer kernel"
+        except Exception as e:  # noqa: BLE001 - no peer access / symmetric memory on this box
+            if os.environ.get("WS_ALLREDUCE", "") == "symm":
+                raise
+            print("wheat_3dgs_b200.dist: symmetric memory unavailable (%s); NCCL all_reduce" % str(e)[:200], flush=True)
+    t = torch.empty((numel,), dtype=torch.float32, device=device)
+
+    def reduce(n=None):
+        if world_size() > 1:
+            dist.all_reduce(t if n is None else t[:n], op=dist.ReduceOp.SUM)
+        return t
+    return t, reduce, "NCCL all_reduce"
+
+
 def allreduce_votes(used_count, async_op=False):
     """SUM over ranks of the label-vote accumulator used_count[(num_obj+1), P]."""
     if world_size() == 1:

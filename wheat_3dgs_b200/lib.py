@@ -10,7 +10,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 # WHEATSPLAT_LIB: another build of the same library (A/B timing of kernel variants, tools/ab.sh)
 LIB_PATH = os.environ.get("WHEATSPLAT_LIB") or os.path.join(_HERE, "libwheatsplat.so")
 
-WS_ABI_VERSION = 1
+WS_ABI_VERSION = 2
 
 # every symbol include/wheatsplat.h declares (tests check the library exports all of them)
 SYMBOLS = [
@@ -18,7 +18,7 @@ SYMBOLS = [
     "ws_forward_prepare", "ws_forward_render", "ws_backward", "ws_mark_visible", "ws_knn_bytes",
     "ws_knn_dist2", "ws_multi_instance_opt", "ws_sort_bytes", "ws_sort_pairs_u64", "ws_sort_pairs_u32", "ws_set_binning_mode",
     "ws_loss_bytes", "ws_l1_ssim_forward", "ws_l1_ssim_backward", "ws_debug_fetch",
-    "ws_adam_step", "ws_densify_stats",
+    "ws_adam_step", "ws_densify_stats", "ws_allreduce_sum_f32",
     "ws_objeval_bytes", "ws_objeval_prepare", "ws_objeval_bin", "ws_objeval_render",
     "ws_launch_count", "ws_prof_enable", "ws_prof_read", "ws_prof_stage_name", "ws_debug_count_pairs",
 ]
@@ -35,7 +35,8 @@ class WsView(C.Structure):
 class WsGaussians(C.Structure):
     _fields_ = [("P", C.c_int32), ("M", C.c_int32), ("means3D", C.c_void_p), ("shs", C.c_void_p),
                 ("colors_precomp", C.c_void_p), ("opacities", C.c_void_p), ("scales", C.c_void_p),
-                ("rotations", C.c_void_p), ("cov3D_precomp", C.c_void_p)]
+                ("rotations", C.c_void_p), ("cov3D_precomp", C.c_void_p), ("shs_rest", C.c_void_p),
+                ("raw_params", C.c_int32)]
 
 
 class WsFlash(C.Structure):
@@ -47,7 +48,7 @@ class WsFlash(C.Structure):
 class WsGrads(C.Structure):
     _fields_ = [("dL_dmeans2D", C.c_void_p), ("dL_dcolors", C.c_void_p), ("dL_dopacity", C.c_void_p),
                 ("dL_dmeans3D", C.c_void_p), ("dL_dcov3D", C.c_void_p), ("dL_dsh", C.c_void_p),
-                ("dL_dscales", C.c_void_p), ("dL_drotations", C.c_void_p)]
+                ("dL_dscales", C.c_void_p), ("dL_drotations", C.c_void_p), ("dL_dsh_rest", C.c_void_p)]
 
 
 class WsObjSets(C.Structure):
@@ -126,6 +127,8 @@ def load():
                                    vp, sz, i64, vp]
     lib.ws_objeval_render.restype = C.c_int
     lib.ws_objeval_render.argtypes = [C.POINTER(WsView), C.POINTER(WsObjSets), vp, vp, sz, i64, i64, vp, sz, vp, vp]
+    lib.ws_allreduce_sum_f32.restype = C.c_int
+    lib.ws_allreduce_sum_f32.argtypes = [i32, i32, i64, vp, C.POINTER(vp), i32, vp]
     lib.ws_adam_step.restype = C.c_int
     lib.ws_adam_step.argtypes = [i32, C.POINTER(WsAdamGroup), C.c_double, C.c_double, C.c_double, vp]
     lib.ws_densify_stats.restype = C.c_int
