@@ -1,0 +1,96 @@
+"""GPU: the raw-parameter entry (GaussianModel's getters -- exp, normalize, sigmoid, torch.cat of
+features_dc/features_rest, scene/gaussian_model.py:101-121 -- folded into preprocess and its backward) against the
+reference's formulation: the same getters as torch ops feeding the standard rasterizer, gradients by autograd."""
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+
+import cases
+from util import assert_grad, assert_image
+
+pytestmark = pytest.mark.gpu
+
+if torch.cuda.is_available():
+    import wheat_3dgs_b200
+    from wheat_3dgs_b200 import scene
+    from wheat_3dgs_b200.rasterizer import GaussianRasterizationSettings, GaussianRasterizer
+
+t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()
+
+
+def _raw(sc, seed=0):
+    """GaussianModel's raw parameters for a scene of activated values (create_from_pcd, :147-161)."""
+    rng = np.random.default_rng(seed)
+    op = np.clip(sc["opacities"], 1e-6, 1 - 1e-6)
+    raw = {"xyz": sc["means3D"], "f_dc": sc["shs"][:, :1, :], "f_rest": sc["shs"][:, 1:, :],
+           "opacity": np.log(op / (1 - op)), "scaling": np.log(sc["scales"]),
+           "rotation": sc["rotations"] * rng.uniform(0.2, 3.0, (sc["rotations"].shape[0], 1))}
+    return {k: t(v.astype(np.float32)).requires_grad_(True) for k, v in raw.items()}
+
+
+def _settings(cam, deg):
+    return GaussianRasterizationSettings(
+        image_height=cam["image_height"], image_width=cam["image_width"], tanfovx=cam["tanfovx"], tanfovy=cam["tanfovy"],
+        bg=t(cases.BG), scale_modifier=1.0, viewmatrix=t(cam["viewmatrix"]), projmatrix=t(cam["projmatrix"]),
+        sh_degree=deg, campos=t(cam["campos"]), prefiltered=False, debug=False)
+
+
+def _both(sc, cam, deg, lg):
+    rs = _settings(cam, deg)
+    dc, dd, da = t(lg["dL_dcolor"]), t(lg["dL_ddepth"]), t(lg["dL_dalpha"])
+    out = {}
+    for kind in ("getters", "raw"):
+        p = _raw(sc)
+        m2d = torch.zeros_like(p["xyz"], requires_grad=True)
+        if kind == "getters":
+            color, radii, depth, alpha = GaussianRasterizer(rs)(
+                means3D=p["xyz"], means2D=m2d, opacities=torch.sigmoid(p["opacity"]),
+                shs=torch.cat((p["f_dc"], p["f_rest"]), dim=1), scales=torch.exp(p["scaling"]),
+                rotations=F.normalize(p["rotation"]))
+        else:
+            color, radii, depth, alpha = GaussianRasterizer(rs).forward_raw(
+                p["xyz"], m2d, p["f_dc"], p["f_rest"], p["opacity"], p["scaling"], p["rotation"])
+        ((color * dc).sum() + (depth * dd).sum() + (alpha * da).sum()).backward()
+        torch.cuda.synchronize()
+        out[kind] = dict(color=color.detach().cpu().numpy(), depth=depth.detach().cpu().numpy(),
+                         alpha=alpha.detach().cpu().numpy(), radii=radii.cpu().numpy(),
+                         grads={k: v.grad.cpu().numpy() for k, v in p.items()}, m2d=m2d.grad.cpu().numpy())
+    return out
+
+
+@pytest.mark.parametrize("name", ["dgr_sh3", "dgr_deg1"])
+def test_raw_entry_matches_getters_plus_rasterizer(name):
+    sc, cam, lg, deg = cases.dgr_inputs(name)
+    o = _both(sc, cam, deg, lg)
+    a, b = o["raw"], o["getters"]
+    # the in-kernel activations are the float operations torch's CUDA kernels perform: same radii, same pixels
+    assert np.array_equal(a["radii"], b["radii"]), "%d radii differ" % (a["radii"] != b["radii"]).sum()
+    for k in ("color", "depth", "alpha"):
+        assert_image(k, a[k], b[k])
+        assert np.array_equal(a[k].view(np.uint32), b[k].view(np.uint32)), k + " is not bit-identical"
+    assert_grad("means2D", a["m2d"], b["m2d"])
+    for k in a["grads"]:
+        assert a["grads"][k].shape == b["grads"][k].shape
+        assert_grad(k, a["grads"][k], b["grads"][k])
+
+
+def test_raw_entry_at_training_size_and_degenerate_quaternions():
+    """200 K Gaussians at 1024x768; a few zero quaternions (normalize clamps the norm at 1e-12) and extreme logits."""
+    P, W, H = 200000, 1024, 768
+    sc = scene.synthetic_scene(P, seed=1)
+    sc["rotations"][:50] = 0.0
+    sc["opacities"][50:100] = 1.0 - 1e-7
+    cam = scene.overhead_cameras(W, H)[9]
+    lg = scene.loss_gradients((3, H, W), seed=2)
+    o = _both(sc, cam, 3, lg)
+    a, b = o["raw"], o["getters"]
+    b2 = _both(sc, cam, 3, lg)["getters"]   # the blend backward sums with float atomics: its own run-to-run spread
+    assert (a["radii"] != b["radii"]).sum() == 0
+    for k in ("color", "depth", "alpha"):
+        assert_image(k, a[k], b[k])
+        assert np.array_equal(a[k].view(np.uint32), b[k].view(np.uint32)), k + " is not bit-identical"
+    for k in a["grads"]:
+        assert np.all(np.isfinite(a["grads"][k]))
+        spread = float(np.abs(b["grads"][k] - b2["grads"][k]).max())
+        assert_grad(k, a["grads"][k], b["grads"][k], spread=spread)

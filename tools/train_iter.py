@@ -1,6 +1,7 @@
 """One full training iteration of train_vanilla_3dgs.py:65-112 on config 2 (1 M Gaussians SH3, 2048x1536,
 36 views), timed with CUDA events, two stacks on the same GPU and the same raw parameters:
 
+  ours-raw   as ours, but the getters (exp / sigmoid / normalize / cat) run inside preprocess (forward_raw)
   ours       torch activations -> drop-in GaussianRasterizer (libwheatsplat) -> fused L1+SSIM loss (ws_loss.cu)
              -> backward -> fused densification statistics + fused Adam (ws_optim.cu)
   reference  torch activations -> UNMODIFIED reference rasterizer (oracle/_ref/libref_dgr.so behind an autograd
@@ -90,11 +91,11 @@ class Trainer:
         self.kind = kind
         self.p = raw_params()
         groups = [{"params": [self.p[n]], "lr": lr, "name": n} for n, lr in LRS]
-        self.opt = (woptim.Adam if kind == "ours" else torch.optim.Adam)(groups, lr=0.0, eps=1e-15)
+        self.opt = (woptim.Adam if kind.startswith("ours") else torch.optim.Adam)(groups, lr=0.0, eps=1e-15)
         self.max_radii2D = torch.zeros(P, device=dev)
         self.accum = torch.zeros(P, 1, device=dev)
         self.denom = torch.zeros(P, 1, device=dev)
-        if kind == "ours":
+        if kind.startswith("ours"):
             wheat_3dgs_b200.install()
             from diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianRasterizer
             self.RS, self.R = GaussianRasterizationSettings, GaussianRasterizer
@@ -107,6 +108,26 @@ class Trainer:
         mark = (lambda name: ev.append((name, self._rec()))) if ev is not None else (lambda name: None)
         c = cd[i % len(cd)]
         gt = gts[i % len(gts)]
+        if self.kind == "ours-raw":
+            means2D = torch.zeros_like(self.p["xyz"], requires_grad=True)
+            mark("activations")
+            rs = self.RS(image_height=H, image_width=W, tanfovx=c["tanfovx"], tanfovy=c["tanfovy"], bg=bg,
+                         scale_modifier=1.0, viewmatrix=c["viewmatrix"], projmatrix=c["projmatrix"], sh_degree=DEG,
+                         campos=c["campos"], prefiltered=False, debug=False)
+            p = self.p
+            image, radii, depth, alpha = self.R(rs).forward_raw(p["xyz"], means2D, p["f_dc"], p["f_rest"], p["opacity"],
+                                                                p["scaling"], p["rotation"])
+            mark("render_fwd")
+            loss = wloss.l1_ssim_loss(image, gt, 0.2)
+            mark("loss_fwd")
+            loss.backward()
+            mark("backward")
+            woptim.add_densification_stats(radii, means2D.grad, self.max_radii2D, self.accum, self.denom)
+            mark("densify_stats")
+            self.opt.step()
+            self.opt.zero_grad(set_to_none=True)
+            mark("adam")
+            return loss
         a = activations(self.p)
         means2D = torch.zeros_like(a["means3D"], requires_grad=True)
         mark("activations")
@@ -175,5 +196,6 @@ def run(kind):
 
 if __name__ == "__main__":
     a = run("ours")
+    r = run("ours-raw")
     b = run("reference")
-    print("full-iteration speed-up x%.2f" % (b / a))
+    print("full-iteration speed-up x%.2f (drop-in API), x%.2f (raw-parameter entry)" % (b / a, b / r))

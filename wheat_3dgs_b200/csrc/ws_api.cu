@@ -116,6 +116,10 @@ int check_view_gauss(const char *who, const ws_view *v, const ws_gaussians *g, b
         set_error("%s: provide exactly one of scale/rotation pair or precomputed 3D covariance", who);
         return WS_E_INVALID;
     }
+    if (g->shs_rest && (!has_sh || g->M < 2)) {
+        set_error("%s: shs_rest needs shs (features_dc) and M >= 2 coefficients in total", who);
+        return WS_E_INVALID;
+    }
     if (v->sh_degree < 0 || v->sh_degree > 3) { set_error("%s: sh_degree must be 0..3", who); return WS_E_INVALID; }
     if (has_sh && (v->sh_degree + 1) * (v->sh_degree + 1) > g->M) {
         set_error("%s: sh_degree %d needs %d coefficients, sh has %d", who, v->sh_degree,

@@ -41,6 +41,9 @@ struct PreBwdParams {
     float *dL_dmeans2D, *dL_dcolors, *dL_dopacity, *dL_dmeans3D, *dL_dcov3D, *dL_dsh, *dL_dscales,
         *dL_drotations;
     int sh_vec4;
+    const float *shs_rest;   // features_rest [P,M-1,3] (shs = features_dc) or NULL
+    float *dL_dsh_rest;      // its gradient
+    int raw;                 // scales/rotations/opacities are raw parameters: chain through exp/normalize/sigmoid
 };
 
 struct F3 { float x, y, z; };
@@ -125,6 +128,19 @@ __global__ void __launch_bounds__(WS_PRE_THREADS) preprocess_bwd(const PreBwdPar
                 int g = i / row4, c = i - g * row4;
                 s_sh4[g * srow4 + c] = __ldg(src + i);
             }
+        } else if (p.shs_rest) {
+            const int rest_f = row_f - 3;
+            const float *src = p.shs + (size_t)base * 3;
+            for (int i = tid; i < nvalid * 3; i += WS_PRE_THREADS) {
+                int g = i / 3, c = i - g * 3;
+                s_sh[g * srow + c] = __ldg(src + i);
+            }
+            src = p.shs_rest + (size_t)base * rest_f;
+            const int n = nvalid * rest_f;
+            for (int i = tid; i < n; i += WS_PRE_THREADS) {
+                int g = i / rest_f, c = i - g * rest_f;
+                s_sh[g * srow + 3 + c] = __ldg(src + i);
+            }
         } else {
             const float *src = p.shs + (size_t)base * row_f;
             const int n = nvalid * row_f;
@@ -158,14 +174,20 @@ __global__ void __launch_bounds__(WS_PRE_THREADS) preprocess_bwd(const PreBwdPar
             const float mx = p.means3D[3 * (size_t)idx], my = p.means3D[3 * (size_t)idx + 1],
                         mz = p.means3D[3 * (size_t)idx + 2];
             float s[3] = {0.f, 0.f, 0.f}, q[4] = {0.f, 0.f, 0.f, 0.f}, c3[6];
+            float qn = 1.0f, qn_raw = 1.0f; // raw parameters: max(|q|, eps) and |q|
             if (p.cov3D_precomp) {
 #pragma unroll
                 for (int k = 0; k < 6; k++) c3[k] = p.cov3D_precomp[6 * (size_t)idx + k];
             } else {
-                const float4 qq = reinterpret_cast<const float4 *>(p.rotations)[idx];
+                float4 qq = reinterpret_cast<const float4 *>(p.rotations)[idx];
+                float s0 = p.scales[3 * (size_t)idx], s1 = p.scales[3 * (size_t)idx + 1], s2 = p.scales[3 * (size_t)idx + 2];
+                if (p.raw) {
+                    qn = raw_quat_norm(qq);
+                    qn_raw = sqrtf(qq.x * qq.x + qq.y * qq.y + qq.z * qq.z + qq.w * qq.w);
+                    raw_activate(qq, s0, s1, s2);
+                }
                 q[0] = qq.x; q[1] = qq.y; q[2] = qq.z; q[3] = qq.w;
-#pragma unroll
-                for (int k = 0; k < 3; k++) s[k] = p.scale_modifier * p.scales[3 * (size_t)idx + k];
+                s[0] = p.scale_modifier * s0; s[1] = p.scale_modifier * s1; s[2] = p.scale_modifier * s2;
                 cov3d_plain(s, q, c3);
             }
             // ---- computeCov2DCUDA, DGR backward.cu:144-274 ----
@@ -318,6 +340,20 @@ __global__ void __launch_bounds__(WS_PRE_THREADS) preprocess_bwd(const PreBwdPar
                 dmean[2] += (-dox * doz * ddx - doy * doz * ddy + (sum2 - doz * doz) * ddz) * invsum32;
             }
             if (!p.cov3D_precomp) cov3d_backward(s, q, dcov, dscale, drot);
+            if (p.raw) {
+                // exp: d/dx = exp(x) = the activated scale; sigmoid: o (1 - o); normalize: (g - q^ (q^ . g)) / |q|
+                // (below the clamp the norm is the constant eps: g / eps, as torch's clamp_min backward)
+                if (!p.cov3D_precomp) {
+                    const float inv_mod = p.scale_modifier != 0.f ? 1.0f / p.scale_modifier : 0.f;
+#pragma unroll
+                    for (int k = 0; k < 3; k++) dscale[k] *= s[k] * inv_mod;
+                    const float qg = qn_raw < 1e-12f ? 0.f : q[0] * drot[0] + q[1] * drot[1] + q[2] * drot[2] + q[3] * drot[3];
+#pragma unroll
+                    for (int k = 0; k < 4; k++) drot[k] = (drot[k] - q[k] * qg) / qn;
+                }
+                const float o = p.g1[idx].y;
+                a[9] *= o * (1.0f - o);
+            }
         } else {
 #pragma unroll
             for (int k = 0; k < 12; k++) a[k] = 0.f;
@@ -350,6 +386,19 @@ __global__ void __launch_bounds__(WS_PRE_THREADS) preprocess_bwd(const PreBwdPar
                 int g = i / row4, c = i - g * row4;
                 dst[i] = s_sh4[g * srow4 + c];
             }
+        } else if (p.shs_rest) {
+            const int rest_f = row_f - 3;
+            float *dst = p.dL_dsh + (size_t)base * 3;
+            for (int i = tid; i < nvalid * 3; i += WS_PRE_THREADS) {
+                int g = i / 3, c = i - g * 3;
+                dst[i] = s_sh[g * srow + c];
+            }
+            dst = p.dL_dsh_rest + (size_t)base * rest_f;
+            const int n = nvalid * rest_f;
+            for (int i = tid; i < n; i += WS_PRE_THREADS) {
+                int g = i / rest_f, c = i - g * rest_f;
+                dst[i] = s_sh[g * srow + 3 + c];
+            }
         } else {
             float *dst = p.dL_dsh + (size_t)base * row_f;
             const int n = nvalid * row_f;
@@ -379,7 +428,12 @@ int launch_preprocess_bwd(const ws_view *v, const ws_gaussians *g, const int32_t
     p.dL_dscales = gr->dL_dscales; p.dL_drotations = gr->dL_drotations;
     const int row_f = 3 * g->M;
     const bool use_sh = g->shs != nullptr && g->M > 0;
-    p.sh_vec4 = (use_sh && row_f % 4 == 0 && ((uintptr_t)g->shs % 16) == 0 &&
+    p.shs_rest = use_sh ? g->shs_rest : nullptr; p.dL_dsh_rest = gr->dL_dsh_rest; p.raw = g->raw_params;
+    if (p.shs_rest && gr->dL_dsh && !gr->dL_dsh_rest) {
+        set_error("preprocess backward: shs_rest given without dL_dsh_rest");
+        return WS_E_INVALID;
+    }
+    p.sh_vec4 = (use_sh && !p.shs_rest && row_f % 4 == 0 && ((uintptr_t)g->shs % 16) == 0 &&
                  (!gr->dL_dsh || ((uintptr_t)gr->dL_dsh % 16) == 0)) ? 1 : 0;
     size_t smem = 0;
     if (use_sh)

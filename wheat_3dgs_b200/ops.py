@@ -47,7 +47,7 @@ class _Call:
 
     def __init__(self, bg, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp,
                  viewmatrix, projmatrix, tanfovx, tanfovy, image_height, image_width, sh, degree, campos,
-                 prefiltered, debug):
+                 prefiltered, debug, sh_rest=None, raw=False):
         if means3D.dim() != 2 or means3D.size(1) != 3:  # DGR rasterize_points.cu:57-59
             raise RuntimeError("means3D must have dimensions (num_points, 3)")
         self.P = means3D.size(0)
@@ -57,15 +57,21 @@ class _Call:
             opacity=_f32c(opacity, "opacities"), scales=_f32c(scales, "scales"),
             rotations=_f32c(rotations, "rotations"), cov3D=_f32c(cov3D_precomp, "cov3D_precomp"),
             view=_f32c(viewmatrix, "viewmatrix"), proj=_f32c(projmatrix, "projmatrix"), sh=_f32c(sh, "sh"),
-            campos=_f32c(campos, "campos"))
+            campos=_f32c(campos, "campos"), sh_rest=_f32c(sh_rest, "features_rest"))
         k = self.keep
         self.M = 0 if k["sh"] is None else k["sh"].size(1)  # DGR rasterize_points.cu:85-89
+        if k["sh_rest"] is not None:
+            if k["sh"] is None or k["sh"].size(1) != 1:
+                raise RuntimeError("features_rest needs features_dc of shape [P,1,3]")
+            self.M = 1 + k["sh_rest"].size(1)
+        self.raw = bool(raw)
         self.device = means3D.device
         self.view = WsView(self.H, self.W, float(tanfovx), float(tanfovy), float(scale_modifier), int(degree),
                            int(bool(prefiltered)), int(bool(debug)), _ptr(k["bg"]), _ptr(k["view"]),
                            _ptr(k["proj"]), _ptr(k["campos"]))
         self.gauss = WsGaussians(self.P, self.M, _ptr(k["means3D"]), _ptr(k["sh"]), _ptr(k["colors"]),
-                                 _ptr(k["opacity"]), _ptr(k["scales"]), _ptr(k["rotations"]), _ptr(k["cov3D"]))
+                                 _ptr(k["opacity"]), _ptr(k["scales"]), _ptr(k["rotations"]), _ptr(k["cov3D"]),
+                                 _ptr(k["sh_rest"]), int(self.raw))
 
 
 def _forward(call, flash):
@@ -128,9 +134,11 @@ def _backward(call, radii, geom, binning, image, R, alpha, dL_dcolor, dL_ddepth,
         views.append(bucket[off:off + s * P])
         off += s * P
     g_means3D, g_means2D, g_sh, g_opac, g_scales, g_rot, g_colors, g_cov = views
+    split = call.keep.get("sh_rest") is not None   # dL_dsh = [features_dc P*3 | features_rest P*3(M-1)]
     grads = WsGrads(g_means2D.data_ptr(), g_colors.data_ptr(), g_opac.data_ptr(), g_means3D.data_ptr(),
                     g_cov.data_ptr(), g_sh.data_ptr() if M > 0 else None,
-                    g_scales.data_ptr() if has_sr else None, g_rot.data_ptr() if has_sr else None)
+                    g_scales.data_ptr() if has_sr else None, g_rot.data_ptr() if has_sr else None,
+                    g_sh[3 * P:].data_ptr() if split else None)
     dc, dd, da = _f32c(dL_dcolor, "dL_dout_color"), _f32c(dL_ddepth, "dL_dout_depth"), _f32c(dL_dalpha, "dL_dout_alpha")
     al = _f32c(alpha, "alphas")
     fl = C.byref(flash) if flash is not None else None
@@ -141,6 +149,9 @@ def _backward(call, radii, geom, binning, image, R, alpha, dL_dcolor, dL_ddepth,
     if not has_sr:
         g_scales.zero_()
         g_rot.zero_()
+    if split:
+        return (g_means2D.view(P, 3), g_colors.view(P, 3), g_opac.view(P, 1), g_means3D.view(P, 3), g_cov.view(P, 6),
+                (g_sh[:3 * P].view(P, 1, 3), g_sh[3 * P:].view(P, M - 1, 3)), g_scales.view(P, 3), g_rot.view(P, 4))
     return (g_means2D.view(P, 3), g_colors.view(P, 3), g_opac.view(P, 1), g_means3D.view(P, 3), g_cov.view(P, 6),
             g_sh.view(P, M, 3), g_scales.view(P, 3), g_rot.view(P, 4))
 
@@ -162,6 +173,42 @@ def rasterize_gaussians_backward(bg, means3D, radii, colors, scales, rotations, 
                  viewmatrix, projmatrix, tanfovx, tanfovy, H, W, sh, degree, campos, False, debug)
     return _backward(call, radii, geomBuffer, binningBuffer, imageBuffer, R, alphas, dL_dout_color,
                      dL_dout_depth, dL_dout_alpha, None, _bucket)
+
+
+def rasterize_gaussians_raw(bg, xyz, features_dc, features_rest, opacity, scaling, rotation, scale_modifier, viewmatrix,
+                            projmatrix, tanfovx, tanfovy, image_height, image_width, degree, campos, debug):
+    """rasterize_gaussians on GaussianModel's RAW parameters: the getters of
+    scene/gaussian_model.py:101-121 (exp, normalize, sigmoid, torch.cat of the two feature tensors) run inside
+    preprocess.  Same 8-tuple as rasterize_gaussians."""
+    call = _Call(bg, xyz, None, opacity, scaling, rotation, scale_modifier, None, viewmatrix, projmatrix, tanfovx,
+                 tanfovy, image_height, image_width, features_dc, degree, campos, False, debug, sh_rest=features_rest,
+                 raw=True)
+    if call.P == 0:
+        dev = xyz.device
+        z = lambda *s: torch.zeros(s, dtype=torch.float32, device=dev)
+        e = torch.empty((0,), dtype=torch.uint8, device=dev)
+        return 0, z(3, call.H, call.W), z(1, call.H, call.W), z(1, call.H, call.W), \
+            torch.zeros((0,), dtype=torch.int32, device=dev), e, e.clone(), e.clone()
+    return _forward(call, None)
+
+
+def rasterize_gaussians_raw_backward(bg, xyz, radii, features_dc, features_rest, scaling, rotation, scale_modifier,
+                                     viewmatrix, projmatrix, tanfovx, tanfovy, dL_dout_color, dL_dout_depth,
+                                     dL_dout_alpha, degree, campos, geomBuffer, R, binningBuffer, imageBuffer, alphas,
+                                     debug, _bucket=None):
+    """Gradients w.r.t. the raw parameters: (dL_dmeans2D, dL_dopacity, dL_dxyz, dL_dfeatures_dc, dL_dfeatures_rest,
+    dL_dscaling, dL_drotation)."""
+    H, W = dL_dout_color.size(1), dL_dout_color.size(2)
+    P = xyz.size(0)
+    if P == 0:
+        z = lambda *s: torch.zeros(s, dtype=torch.float32, device=xyz.device)
+        return z(0, 3), z(0, 1), z(0, 3), z(0, 1, 3), z(0, features_rest.size(1), 3), z(0, 3), z(0, 4)
+    call = _Call(bg, xyz, None, None, scaling, rotation, scale_modifier, None, viewmatrix, projmatrix, tanfovx, tanfovy,
+                 H, W, features_dc, degree, campos, False, debug, sh_rest=features_rest, raw=True)
+    g2d, _, gop, gxyz, _, (gdc, grest), gsc, grot = _backward(call, radii, geomBuffer, binningBuffer, imageBuffer, R,
+                                                             alphas, dL_dout_color, dL_dout_depth, dL_dout_alpha, None,
+                                                             _bucket)
+    return g2d, gop, gxyz, gdc, grest, gsc, grot
 
 
 def mark_visible(means3D, viewmatrix, projmatrix):

@@ -148,6 +148,44 @@ class _Rasterize(torch.autograd.Function):
                 opt(g_scales, scales), opt(g_rot, rotations), opt(g_cov3D, cov3Ds_precomp), None)
 
 
+class _RasterizeRaw(torch.autograd.Function):
+    """forward(ctx, xyz, means2D, features_dc, features_rest, opacity, scaling, rotation, raster_settings) on
+    GaussianModel's raw parameters; the activations and their backward run inside the kernels."""
+
+    @staticmethod
+    def forward(ctx, xyz, means2D, features_dc, features_rest, opacity, scaling, rotation, rs):
+        args = (rs.bg, xyz, features_dc, features_rest, opacity, scaling, rotation, rs.scale_modifier, rs.viewmatrix,
+                rs.projmatrix, rs.tanfovx, rs.tanfovy, rs.image_height, rs.image_width, rs.sh_degree, rs.campos, rs.debug)
+        R, color, depth, alpha, radii, geom, binning, image = _guarded(ops.rasterize_gaussians_raw, args, rs.debug,
+                                                                       "snapshot_fw.dump", "forward")
+        ctx.rs, ctx.num_rendered = rs, R
+        ctx.save_for_backward(xyz, features_dc, features_rest, scaling, rotation, radii, geom, binning, image, alpha)
+        ctx.mark_non_differentiable(radii)
+        return color, radii, depth, alpha
+
+    @staticmethod
+    def backward(ctx, grad_color, grad_radii, grad_depth, grad_alpha):
+        rs = ctx.rs
+        xyz, features_dc, features_rest, scaling, rotation, radii, geom, binning, image, alpha = ctx.saved_tensors
+        H, W, dev = rs.image_height, rs.image_width, xyz.device
+        z = lambda c: torch.zeros((c, H, W), dtype=torch.float32, device=dev)
+        grad_color = z(3) if grad_color is None else grad_color
+        grad_depth = z(1) if grad_depth is None else grad_depth
+        grad_alpha = z(1) if grad_alpha is None else grad_alpha
+        args = (rs.bg, xyz, radii, features_dc, features_rest, scaling, rotation, rs.scale_modifier, rs.viewmatrix,
+                rs.projmatrix, rs.tanfovx, rs.tanfovy, grad_color, grad_depth, grad_alpha, rs.sh_degree, rs.campos, geom,
+                ctx.num_rendered, binning, image, alpha, rs.debug)
+        fn = ops.rasterize_gaussians_raw_backward
+        if _GRAD_BUCKET is not None:
+            fn = lambda *a: ops.rasterize_gaussians_raw_backward(*a, _bucket=_GRAD_BUCKET)  # noqa: E731
+        g2d, gop, gxyz, gdc, grest, gsc, grot = _guarded(fn, args, rs.debug, "snapshot_bw.dump", "backward")
+        return gxyz, g2d, gdc, grest, gop, gsc, grot, None
+
+
+def rasterize_gaussians_raw(xyz, means2D, features_dc, features_rest, opacity, scaling, rotation, raster_settings):
+    return _RasterizeRaw.apply(xyz, means2D, features_dc, features_rest, opacity, scaling, rotation, raster_settings)
+
+
 def rasterize_gaussians(means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
                         raster_settings):
     """diff_gaussian_rasterization.rasterize_gaussians (DGR __init__.py:21-42)."""
@@ -193,6 +231,17 @@ class GaussianRasterizer(nn.Module):
         return rasterize_gaussians(means3D, means2D, _or_empty(shs), _or_empty(colors_precomp), opacities,
                                    _or_empty(scales), _or_empty(rotations), _or_empty(cov3D_precomp),
                                    self.raster_settings)
+
+
+def _forward_raw(self, xyz, means2D, features_dc, features_rest, opacity, scaling, rotation):
+    """Extension (not in the reference API): render GaussianModel's RAW parameters -- `_xyz`, `_features_dc`,
+    `_features_rest`, `_opacity`, `_scaling`, `_rotation` (scene/gaussian_model.py:147-161) -- with the getters'
+    activations (:101-121) and their backward folded into the kernels.  Returns color, radii, depth, alpha."""
+    return rasterize_gaussians_raw(xyz, means2D, features_dc, features_rest, opacity, scaling, rotation,
+                                   self.raster_settings)
+
+
+GaussianRasterizer.forward_raw = _forward_raw
 
 
 class FlashGaussianRasterizer(nn.Module):
