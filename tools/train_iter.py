@@ -195,6 +195,9 @@ def run(kind):
 
 
 if __name__ == "__main__":
+    if len(sys.argv) > 2:            # one stack only (profiling target): python tools/train_iter.py 3 ours-raw
+        run(sys.argv[2])
+        sys.exit(0)
     a = run("ours")
     r = run("ours-raw")
     b = run("reference")
