@@ -241,13 +241,21 @@ __global__ void __launch_bounds__(MG_THREADS) objeval_merge(int num_rows, const 
             __stcg(&mine[blockIdx.x].smin, a); __stcg(&mine[blockIdx.x].sren, b); __stcg(&mine[blockIdx.x].cnt, c);
         }
         grid_barrier(&sync->arrive, target);
-        if (tid == 0) {
+        if (wid == 0) {
+            // warp 0 adds the per-CTA partials: lane l takes CTAs l, l+32, ... then a fixed shuffle tree -- the same
+            // order in every CTA and every run (a serial loop of L2 round trips cost ~30 us per object)
             int c = 0; double a = 0.0, b = 0.0;
-            for (unsigned k = 0; k < gridDim.x; k++) {
+            for (unsigned k = lane; k < gridDim.x; k += 32) {
                 c += __ldcg(&mine[k].cnt); a += __ldcg(&mine[k].smin); b += __ldcg(&mine[k].sren);
             }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                c += __shfl_xor_sync(0xffffffffu, c, o);
+                a += __shfl_xor_sync(0xffffffffu, a, o);
+                b += __shfl_xor_sync(0xffffffffu, b, o);
+            }
             // min_depth[overlap].mean() < render_depth[overlap].mean(), float32 means
-            s_behind = (c > 0 && (float)(a / (double)c) < (float)(b / (double)c)) ? 1 : 0;
+            if (lane == 0) s_behind = (c > 0 && (float)(a / (double)c) < (float)(b / (double)c)) ? 1 : 0;
         }
         __syncthreads();
         const bool behind = s_behind != 0;

@@ -74,6 +74,39 @@ class _Call:
                                  _ptr(k["sh_rest"]), int(self.raw))
 
 
+_BIN_GRANULE = 64 << 20
+_BIN_POOL = {}   # (device, stream) -> [uint8 base tensors]
+_USE_COUNT = getattr(torch._C, "_storage_Use_Count", None)
+
+
+def _in_use(base):
+    # references to the storage besides the pool's tensor and the temporary made here: views handed out earlier that
+    # are still alive in Python or saved in an autograd graph
+    return _USE_COUNT(base.untyped_storage()._cdata) > 2
+
+
+def _binning_alloc(nbytes, dev):
+    """The instance-list scratch changes size with every view (R is data dependent) and is the largest allocation
+    of a step (~0.5 GB at config 2).  Asking torch's caching allocator for a different size every view fragments
+    its pool and ends in cudaMalloc/cudaFree calls (device synchronisations) inside the training loop, so the
+    scratch comes from a small grow-only pool per (device, stream): a buffer is handed out again (as a view) once
+    nothing references its storage any more -- neither Python nor a saved-for-backward slot of an autograd graph."""
+    if nbytes <= 0:
+        return torch.empty((0,), dtype=torch.uint8, device=dev)
+    if _USE_COUNT is None:
+        return torch.empty(((nbytes + _BIN_GRANULE - 1) // _BIN_GRANULE * _BIN_GRANULE,), dtype=torch.uint8, device=dev)
+    key = (str(dev), torch.cuda.current_stream(dev).cuda_stream)
+    pool = _BIN_POOL.setdefault(key, [])
+    for base in pool:
+        if base.numel() >= nbytes and not _in_use(base):
+            return base.narrow(0, 0, nbytes)
+    pool[:] = [b for b in pool if _in_use(b)]   # unused but too small: give them back to the allocator
+    want = (int(nbytes * 1.25) + _BIN_GRANULE - 1) // _BIN_GRANULE * _BIN_GRANULE
+    base = torch.empty((want,), dtype=torch.uint8, device=dev)
+    pool.append(base)
+    return base.narrow(0, 0, nbytes)
+
+
 def _forward(call, flash):
     """Shared forward: returns (R, color, depth, alpha, radii, geom, binning, image)."""
     L = _lib.load()
@@ -91,7 +124,7 @@ def _forward(call, flash):
         st = _stream()
         R = _lib.check(L.ws_forward_prepare(C.byref(call.view), C.byref(call.gauss), radii.data_ptr(),
                                             geom.data_ptr(), geom.numel(), fl, st), "ws_forward_prepare")
-        binning = torch.empty((L.ws_binning_bytes(R, W, H) if R > 0 else 0,), **u8)
+        binning = _binning_alloc(L.ws_binning_bytes(R, W, H) if R > 0 else 0, dev)
         _lib.check(L.ws_forward_render(C.byref(call.view), C.byref(call.gauss), radii.data_ptr(), geom.data_ptr(),
                                        _ptr(binning), binning.numel(), image.data_ptr(), image.numel(), R,
                                        color.data_ptr(), depth.data_ptr(), alpha.data_ptr(), fl, st),

@@ -108,7 +108,7 @@ def eval_obj_labels_tensors(sets, raster_settings, means3D, opacities, shs=None,
         st = _ops._stream()
         R = _lib.check(L.ws_objeval_prepare(C.byref(call.view), C.byref(call.gauss), C.byref(ws), radii.data_ptr(),
                                             geom.data_ptr(), geom.numel(), st), "ws_objeval_prepare")
-        binning = torch.empty((L.ws_binning_bytes(R, W, H) if R > 0 else 0,), **u8)
+        binning = _ops._binning_alloc(L.ws_binning_bytes(R, W, H) if R > 0 else 0, dev)
         scratch = torch.empty((L.ws_objeval_bytes(sets.num_rows, W, H, R),), **u8)
         J = _lib.check(L.ws_objeval_bin(C.byref(call.view), C.byref(call.gauss), C.byref(ws), radii.data_ptr(),
                                         geom.data_ptr(), _ops._ptr(binning), binning.numel(), scratch.data_ptr(),
