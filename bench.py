@@ -228,7 +228,18 @@ def run_ours(args, rank, world, local):
     bucket, reduce_bucket, reduce_how = wdist.make_bucket(wdist.full_bucket_numel(P, M), dev)
     n_train = wdist.train_bucket_numel(P, M)
 
+    # N > 1: views of similar cost (instance count R, from an untimed pass: preprocess + scan only) share a step,
+    # because the step lasts as long as its slowest view (dist.balanced_schedule).  N = 1: plain round robin.
+    schedule = None
+    if world > 1:
+        costs = [ops.count_instances(bg, g["means3D"], g["opacities"], g["scales"], g["rotations"], c["viewmatrix"],
+                                     c["projmatrix"], c["tanfovx"], c["tanfovy"], H, W, g["shs"], SH_DEGREE, c["campos"])
+                 for c in cd]
+        schedule = wdist.balanced_schedule(costs, world, 2 * (args.steps + args.warmup) + 64)
+
     def view_of(i):
+        if schedule is not None:
+            return schedule[i % len(schedule)][rank]
         return (rank + i * world) % nv
 
     def fwd(c):
@@ -261,8 +272,10 @@ def run_ours(args, rank, world, local):
         step(i)
     barrier()
     clk = ClockSampler(local)
-    clk.start()
-    clk.wait_started()
+    if rank == 0:   # one sampler per job: eight nvidia-smi pollers contend for the driver and slow every rank's launches
+        clk.start()
+        clk.wait_started()
+    barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     n0 = ops.launch_count()
     t0 = time.time()
@@ -465,8 +478,8 @@ def main():
     metric = METRIC if args.workload == "cfg2" else "train views/s (rasterizer fwd+bwd per view, %s)" % args.workload
     config = {"workload": "%s: synthetic plot_461-shaped scene, P=%d Gaussians SH3, %d overhead views %dx%d, fwd+bwd "
                           "per view" % (args.workload, P, nv, W, H),
-              "views_per_step_per_gpu": 1, "parallelism": "views sharded x%d, Gaussians replicated, 1 all_reduce of "
-              "62*P fp32 per step" % world if world > 1 else "single GPU",
+              "views_per_step_per_gpu": 1, "parallelism": "views sharded x%d (views of similar instance count share a step), Gaussians "
+              "replicated, 1 in-place SUM of 62*P fp32 per step" % world if world > 1 else "single GPU",
               "l2": "per-step inputs (236 MB Gaussians + 600 MB instance lists) exceed the 126 MB L2; no flush"}
     base = {"metric": metric, "unit": "views/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
@@ -475,7 +488,11 @@ def main():
     if args.impl != "ours":
         if rank != 0:
             return 0
-        line = dict(base, impl="reference", n_gpus=1)
+        # the reference is single-GPU (utils/general_utils.py:133): under torchrun rank 0 alone runs it; n_gpus is the
+        # launch's N so that the line pairs with this arm's line of the same N
+        line = dict(base, impl="reference", n_gpus=world,
+                    config=dict(config, parallelism="reference is single-GPU: one view per step on rank 0"
+                                + (" (launched with %d ranks, the others idle)" % world if world > 1 else "")))
         if args.impl == "reference":
             sys.path.insert(0, os.path.join(ROOT, "oracle"))
             import ref as refmod

@@ -162,3 +162,17 @@ def test_view_sharding_and_bucket_layout():
     assert s["dL_dmeans3D"].shape == (P, 3) and s["dL_dsh"].shape == (P, M, 3) and s["dL_dcov3D"].shape == (P, 6)
     assert s["dL_dmeans3D"][0, 0] == 0 and s["dL_dmeans2D"][0, 0] == 3 * P and s["dL_dcolors"][0, 0] == 62 * P
     assert wdist.world_size() == 1 and wdist.allreduce_train_grads(b, P, M) is None
+
+
+def test_balanced_schedule_groups_views_of_similar_cost():
+    from wheat_3dgs_b200 import dist as wdist
+    costs = [5.0, 9.0, 1.0, 7.0, 3.0, 8.0, 2.0, 6.0]
+    sched = wdist.balanced_schedule(costs, 4, 6)
+    assert sched[0] == [1, 5, 3, 7] and sched[1] == [0, 4, 6, 2] and sched[2] == sched[0]
+    # every view is visited equally often over a whole number of cycles, one view per rank and step
+    flat = [v for step in wdist.balanced_schedule(costs, 3, 8) for v in step]
+    assert sorted(flat) == sorted(list(range(8)) * 3)
+    # the spread of costs inside a step is no larger than that of round robin
+    spread = lambda s: max(max(costs[v] for v in st) - min(costs[v] for v in st) for st in s)
+    rr = [[(r + i * 4) % 8 for r in range(4)] for i in range(2)]
+    assert spread(sched[:2]) <= spread(rr)

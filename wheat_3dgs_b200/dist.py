@@ -51,6 +51,17 @@ def shard(units, rank, world):
     return list(units)[rank::world]
 
 
+def balanced_schedule(costs, world, n_steps):
+    """Lock-step data parallelism ends every step with the exchange, so a step lasts as long as its slowest view.
+    Views differ in cost (the instance count R varies by +-25 % over the overhead views), hence views of SIMILAR
+    cost are put into the same step: the views are sorted by cost and dealt out `world` at a time, cycling through
+    the sorted list (every view is visited equally often; a trainer shuffles the ORDER of the steps, not their
+    composition, and refreshes the costs from the previous epoch's R).  Returns schedule[step][rank] = view index."""
+    order = sorted(range(len(costs)), key=lambda v: (-float(costs[v]), v))
+    n = len(order)
+    return [[order[(s * world + r) % n] for r in range(world)] for s in range(n_steps)]
+
+
 def shard_counts(n_units, world):
     """Units per rank of shard(range(n_units), r, world) for every r."""
     return [len(range(r, n_units, world)) for r in range(world)]

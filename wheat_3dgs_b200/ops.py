@@ -244,6 +244,22 @@ def rasterize_gaussians_raw_backward(bg, xyz, radii, features_dc, features_rest,
     return g2d, gop, gxyz, gdc, grest, gsc, grot
 
 
+def count_instances(bg, means3D, opacity, scales, rotations, viewmatrix, projmatrix, tanfovx, tanfovy, image_height,
+                    image_width, sh, degree, campos):
+    """num_rendered (= sum of tiles_touched, the length of the instance list) of a view without rendering it:
+    preprocess + scan only.  The cost estimate dist.balanced_schedule groups views by."""
+    call = _Call(bg, means3D, None, opacity, scales, rotations, 1.0, None, viewmatrix, projmatrix, tanfovx, tanfovy,
+                 image_height, image_width, sh, degree, campos, False, False)
+    if call.P == 0:
+        return 0
+    L = _lib.load()
+    radii = torch.empty((call.P,), dtype=torch.int32, device=call.device)
+    geom = torch.empty((L.ws_geom_bytes(call.P),), dtype=torch.uint8, device=call.device)
+    with torch.cuda.device(call.device):
+        return _lib.check(L.ws_forward_prepare(C.byref(call.view), C.byref(call.gauss), radii.data_ptr(), geom.data_ptr(),
+                                               geom.numel(), None, _stream()), "ws_forward_prepare")
+
+
 def mark_visible(means3D, viewmatrix, projmatrix):
     """= _C.mark_visible (DGR rasterize_points.cu:210-229) -> bool[P]."""
     L = _lib.load()
