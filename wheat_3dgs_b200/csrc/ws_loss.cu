@@ -82,48 +82,75 @@ __global__ void __launch_bounds__(LS_THREADS) ssim_fwd(const LossParams p)
     }
     __syncthreads();
 
-    // horizontal pass: 42 rows x 32 columns
-    for (int i = tid; i < LS_IN * LS_TILE; i += LS_THREADS) {
-        const int r = i / LS_TILE, c = i - r * LS_TILE;
-        float m1 = 0.f, m2 = 0.f, xx = 0.f, yy = 0.f, xy = 0.f;
+    // horizontal pass: 42 rows x 32 columns, FOUR adjacent columns per thread: 14 loads of x and y feed 4 x 11 taps
+    // (the passes are shared-memory bound: one value per tap cost 22 LDS per output, this costs 7)
+    for (int i = tid; i < LS_IN * (LS_TILE / 4); i += LS_THREADS) {
+        const int r = i / (LS_TILE / 4), c0 = (i - r * (LS_TILE / 4)) * 4;
+        float m1[4] = {0.f, 0.f, 0.f, 0.f}, m2[4] = {0.f, 0.f, 0.f, 0.f}, xx[4] = {0.f, 0.f, 0.f, 0.f},
+              yy[4] = {0.f, 0.f, 0.f, 0.f}, xy[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-        for (int k = 0; k < 11; k++) {
-            const float w = c_gauss[k], a = s_x[r][c + k], b = s_y[r][c + k];
-            m1 += w * a; m2 += w * b;
-            xx += w * a * a; yy += w * b * b; xy += w * a * b;
+        for (int kk = 0; kk < 14; kk++) {
+            const float a = s_x[r][c0 + kk], b = s_y[r][c0 + kk];
+            const float aa = a * a, bb = b * b, ab = a * b;
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                const int k = kk - j;
+                if (k >= 0 && k < 11) {
+                    const float w = c_gauss[k];
+                    m1[j] += w * a; m2[j] += w * b; xx[j] += w * aa; yy[j] += w * bb; xy[j] += w * ab;
+                }
+            }
         }
-        s_h[0][r][c] = m1; s_h[1][r][c] = m2; s_h[2][r][c] = xx; s_h[3][r][c] = yy; s_h[4][r][c] = xy;
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            s_h[0][r][c0 + j] = m1[j]; s_h[1][r][c0 + j] = m2[j]; s_h[2][r][c0 + j] = xx[j];
+            s_h[3][r][c0 + j] = yy[j]; s_h[4][r][c0 + j] = xy[j];
+        }
     }
     __syncthreads();
 
     // vertical pass + SSIM map and its partials (utils/loss_utils.py:43-57)
     float sum_m = 0.0f, sum_l1 = 0.0f;
-    for (int i = tid; i < LS_TILE * LS_TILE; i += LS_THREADS) {
-        const int r = i / LS_TILE, c = i - r * LS_TILE;
-        const int gy = y0 + r, gx = x0 + c;
-        if (gy >= p.H || gx >= p.W) continue;
-        float mu1 = 0.f, mu2 = 0.f, exx = 0.f, eyy = 0.f, exy = 0.f;
+    // FOUR adjacent rows per thread: 14 loads per moment feed 4 x 11 taps
+    for (int i = tid; i < (LS_TILE / 4) * LS_TILE; i += LS_THREADS) {
+        const int rg = i / LS_TILE, c = i - rg * LS_TILE, r0 = rg * 4;
+        float acc[5][4];
 #pragma unroll
-        for (int k = 0; k < 11; k++) {
-            const float w = c_gauss[k];
-            mu1 += w * s_h[0][r + k][c]; mu2 += w * s_h[1][r + k][c];
-            exx += w * s_h[2][r + k][c]; eyy += w * s_h[3][r + k][c]; exy += w * s_h[4][r + k][c];
+        for (int m = 0; m < 5; m++) {
+#pragma unroll
+            for (int j = 0; j < 4; j++) acc[m][j] = 0.f;
+#pragma unroll
+            for (int kk = 0; kk < 14; kk++) {
+                const float v = s_h[m][r0 + kk][c];
+#pragma unroll
+                for (int j = 0; j < 4; j++) {
+                    const int k = kk - j;
+                    if (k >= 0 && k < 11) acc[m][j] += c_gauss[k] * v;
+                }
+            }
         }
-        const float C1 = 0.01f * 0.01f, C2 = 0.03f * 0.03f;
-        const float mu1_sq = mu1 * mu1, mu2_sq = mu2 * mu2, mu12 = mu1 * mu2;
-        const float s1 = exx - mu1_sq, s2 = eyy - mu2_sq, s12 = exy - mu12;
-        const float A1 = 2.0f * mu12 + C1, A2 = 2.0f * s12 + C2;
-        const float B1 = mu1_sq + mu2_sq + C1, B2 = s1 + s2 + C2;
-        const float inv = 1.0f / (B1 * B2);
-        const float m = A1 * A2 * inv;
-        // m = A1 A2 / (B1 B2) with sigma terms expanded in (mu1, E[xx], E[xy])
-        const float dmu1 = 2.0f * inv * (mu2 * (A2 - A1) - mu1 * m * (B2 - B1));
-        const float dexx = -m / B2;
-        const float dexy = 2.0f * A1 * inv;
-        const size_t o = poff + (size_t)gy * p.W + gx;
-        p.dm_dmu1[o] = dmu1; p.dm_dexx[o] = dexx; p.dm_dexy[o] = dexy;
-        sum_m += m;
-        sum_l1 += fabsf(s_x[r + LS_HALO][c + LS_HALO] - s_y[r + LS_HALO][c + LS_HALO]);
+        const int gx = x0 + c;
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            const int r = r0 + j, gy = y0 + r;
+            if (gy >= p.H || gx >= p.W) continue;
+            const float mu1 = acc[0][j], mu2 = acc[1][j], exx = acc[2][j], eyy = acc[3][j], exy = acc[4][j];
+            const float C1 = 0.01f * 0.01f, C2 = 0.03f * 0.03f;
+            const float mu1_sq = mu1 * mu1, mu2_sq = mu2 * mu2, mu12 = mu1 * mu2;
+            const float s1 = exx - mu1_sq, s2 = eyy - mu2_sq, s12 = exy - mu12;
+            const float A1 = 2.0f * mu12 + C1, A2 = 2.0f * s12 + C2;
+            const float B1 = mu1_sq + mu2_sq + C1, B2 = s1 + s2 + C2;
+            const float inv = 1.0f / (B1 * B2);
+            const float m = A1 * A2 * inv;
+            // m = A1 A2 / (B1 B2) with sigma terms expanded in (mu1, E[xx], E[xy])
+            const float dmu1 = 2.0f * inv * (mu2 * (A2 - A1) - mu1 * m * (B2 - B1));
+            const float dexx = -m / B2;
+            const float dexy = 2.0f * A1 * inv;
+            const size_t o = poff + (size_t)gy * p.W + gx;
+            p.dm_dmu1[o] = dmu1; p.dm_dexx[o] = dexx; p.dm_dexy[o] = dexy;
+            sum_m += m;
+            sum_l1 += fabsf(s_x[r + LS_HALO][c + LS_HALO] - s_y[r + LS_HALO][c + LS_HALO]);
+        }
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
@@ -193,33 +220,56 @@ __global__ void __launch_bounds__(LS_THREADS) ssim_bwd(const LossBwdParams p)
         s_in[0][r][c] = a; s_in[1][r][c] = b; s_in[2][r][c] = d;
     }
     __syncthreads();
-    for (int i = tid; i < LS_IN * LS_TILE; i += LS_THREADS) {
-        const int r = i / LS_TILE, c = i - r * LS_TILE;
-        float a = 0.f, b = 0.f, d = 0.f;
+    for (int i = tid; i < LS_IN * (LS_TILE / 4); i += LS_THREADS) {   // four adjacent columns per thread
+        const int r = i / (LS_TILE / 4), c0 = (i - r * (LS_TILE / 4)) * 4;
+        float acc[3][4];
 #pragma unroll
-        for (int k = 0; k < 11; k++) {
-            const float w = c_gauss[k];
-            a += w * s_in[0][r][c + k]; b += w * s_in[1][r][c + k]; d += w * s_in[2][r][c + k];
+        for (int m = 0; m < 3; m++) {
+#pragma unroll
+            for (int j = 0; j < 4; j++) acc[m][j] = 0.f;
+#pragma unroll
+            for (int kk = 0; kk < 14; kk++) {
+                const float v = s_in[m][r][c0 + kk];
+#pragma unroll
+                for (int j = 0; j < 4; j++) {
+                    const int k = kk - j;
+                    if (k >= 0 && k < 11) acc[m][j] += c_gauss[k] * v;
+                }
+            }
+#pragma unroll
+            for (int j = 0; j < 4; j++) s_h[m][r][c0 + j] = acc[m][j];
         }
-        s_h[0][r][c] = a; s_h[1][r][c] = b; s_h[2][r][c] = d;
     }
     __syncthreads();
     const float ca = p.coef[p.per_plane ? 2 * plane : 0], cb = p.coef[p.per_plane ? 2 * plane + 1 : 1];
-    for (int i = tid; i < LS_TILE * LS_TILE; i += LS_THREADS) {
-        const int r = i / LS_TILE, c = i - r * LS_TILE;
-        const int gy = y0 + r, gx = x0 + c;
-        if (gy >= p.H || gx >= p.W) continue;
-        float a = 0.f, b = 0.f, d = 0.f;
+    for (int i = tid; i < (LS_TILE / 4) * LS_TILE; i += LS_THREADS) {   // four adjacent rows per thread
+        const int rg = i / LS_TILE, c = i - rg * LS_TILE, r0 = rg * 4;
+        float acc[3][4];
 #pragma unroll
-        for (int k = 0; k < 11; k++) {
-            const float w = c_gauss[k];
-            a += w * s_h[0][r + k][c]; b += w * s_h[1][r + k][c]; d += w * s_h[2][r + k][c];
+        for (int m = 0; m < 3; m++) {
+#pragma unroll
+            for (int j = 0; j < 4; j++) acc[m][j] = 0.f;
+#pragma unroll
+            for (int kk = 0; kk < 14; kk++) {
+                const float v = s_h[m][r0 + kk][c];
+#pragma unroll
+                for (int j = 0; j < 4; j++) {
+                    const int k = kk - j;
+                    if (k >= 0 && k < 11) acc[m][j] += c_gauss[k] * v;
+                }
+            }
         }
-        const size_t o = poff + (size_t)gy * p.W + gx;
-        const float xv = __ldg(p.x + o), yv = __ldg(p.y + o);
-        const float diff = xv - yv;
-        const float sgn = diff > 0.0f ? 1.0f : (diff < 0.0f ? -1.0f : 0.0f); // torch.abs backward: sign
-        p.dL_dx[o] = ca * (a + 2.0f * xv * b + yv * d) + cb * sgn;
+        const int gx = x0 + c;
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            const int gy = y0 + r0 + j;
+            if (gy >= p.H || gx >= p.W) continue;
+            const size_t o = poff + (size_t)gy * p.W + gx;
+            const float xv = __ldg(p.x + o), yv = __ldg(p.y + o);
+            const float diff = xv - yv;
+            const float sgn = diff > 0.0f ? 1.0f : (diff < 0.0f ? -1.0f : 0.0f); // torch.abs backward: sign
+            p.dL_dx[o] = ca * (acc[0][j] + 2.0f * xv * acc[1][j] + yv * acc[2][j]) + cb * sgn;
+        }
     }
 }
 
