@@ -13,7 +13,8 @@ all_reduce of the 62*P-float gradient bucket.
              (ops.rasterize_gaussians + ops.rasterize_gaussians_backward)
   e2e        views/s through the drop-in GaussianRasterizer + autograd, with this step's ground-truth
              image (3xHxW fp32) and camera copied from pinned host memory and the loss read back
-             to the host inside the timed region
+             to the host inside the timed region (each step's 4 bytes are copied behind the step and
+             read one step later, the last before the closing event: ResultReader, both arms)
   roofline   the dominant stage, timed with CUDA events recorded by the library on the launching
              stream in a second pass over the same steps
   cpu_baseline  the CPU oracle (oracle/splat_oracle.c, a port) on a bounded sample, rank 0, N=1
@@ -177,6 +178,39 @@ class InputPrefetcher:
         sl["free"].record()
 
 
+class ResultReader:
+    """The harness's result pipeline, shared by both arms.  Every step's loss (4 bytes) is copied to pinned host
+    memory behind the step's kernels and READ on the host one step later, once the next step has been queued
+    (a training loop's logging, one step delayed), so the device never drains while the host formats a number.
+    Every step's value is read inside the timed region: `flush()` reads the last one before the closing event."""
+
+    def __init__(self, torch):
+        self.torch = torch
+        self.host = torch.empty(2, dtype=torch.float32).pin_memory()
+        self.ev = [torch.cuda.Event(), torch.cuda.Event()]
+        self.pending = None
+        self.n = 0
+        self.values = []
+
+    def push(self, loss):
+        k = self.n & 1
+        self.host[k:k + 1].copy_(loss.detach().reshape(1), non_blocking=True)
+        self.ev[k].record()
+        prev, self.pending = self.pending, k
+        self.n += 1
+        if prev is not None:
+            self._read(prev)
+
+    def _read(self, k):
+        self.ev[k].synchronize()
+        self.values.append(float(self.host[k]))
+
+    def flush(self):
+        if self.pending is not None:
+            self._read(self.pending)
+            self.pending = None
+
+
 def stage_model(P, V, R, T, HW, M, npass, n_eval, n_contrib):
     """Algorithmic HBM bytes / flops per view of every stage (DESIGN.md section 4 derives them)."""
     c = 12 * M  # SH bytes per Gaussian
@@ -322,18 +356,20 @@ def run_ours(args, rank, world, local):
         pre.release(sl)
         if world > 1:
             reduce_bucket(n_train)
-        val = loss.item()  # device -> host read of the step's result
+        res.push(loss)  # device -> host read of the step's result (ResultReader)
         for p_ in list(params.values()) + [means2D]:
             p_.grad = None
-        return val
 
+    res = ResultReader(torch)
     pre.prefetch(0)
     for i in range(args.warmup):
         e2e_step(i, last=False)
+    res.flush()
     barrier()  # (the first timed step's inputs were prefetched during the last warm-up step, as every step's are)
     e0.record()
     for i in range(args.steps):
         e2e_step(args.warmup + i, last=(i == args.steps - 1))
+    res.flush()
     e1.record()
     barrier()
     ms_e2e = wdist.max_over_ranks(e0.elapsed_time(e1), dev)
@@ -423,15 +459,18 @@ def run_reference_cuda(args, local):
         dcol = diff * (2.0 / diff.numel())
         rr.backward(dcol, torch.zeros_like(dd), torch.zeros_like(da), grads=grads)
         pre.release(sl)
-        return loss.item()
+        res.push(loss)
 
+    res = ResultReader(torch)
     pre.prefetch(0)
     for i in range(args.warmup):
         e2e_step(i, last=False)
+    res.flush()
     torch.cuda.synchronize()
     e0.record()
     for i in range(args.steps):
         e2e_step(args.warmup + i, last=(i == args.steps - 1))
+    res.flush()
     e1.record()
     torch.cuda.synchronize()
     ms_e2e = e0.elapsed_time(e1)
