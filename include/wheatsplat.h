@@ -225,6 +225,50 @@ int ws_adam_step(int32_t n_groups, const ws_adam_group *groups, double beta1, do
 int ws_densify_stats(int32_t P, const int32_t *radii, const float *dL_dmeans2D, float *max_radii2D,
                      float *xyz_gradient_accum, float *denom, ws_stream_t stream);
 
+/* GaussianModel.densify_and_prune (scene/gaussian_model.py:440-458: densify_and_clone :420-438, densify_and_split
+ * :392-418, prune_points :327-352, with cat_tensors_to_optimizer :354-374 and _prune_optimizer :310-325) as ONE plan
+ * and ONE gather instead of three rounds of masked indexing + torch.cat over every parameter and Adam moment.
+ * The surviving rows come out in the reference's order:
+ *   [originals that are neither split nor pruned | their clones | first split children | second split children]
+ * ws_densify_plan decides, per Gaussian i of the P present: grads = xyz_gradient_accum/denom (NaN -> 0);
+ *   clone  iff |grads| >= max_grad and max(exp(scaling)) <= dense_scale   (= percent_dense * extent)
+ *   split  iff  grads  >= max_grad and max(exp(scaling)) >  dense_scale
+ *   pruned iff sigmoid(opacity) < min_opacity, or (use_screen != 0 and (0 > max_screen_size or
+ *          max(scale) > big_scale (= 0.1 * extent)))    -- max_radii2D is all zeros when the reference tests it
+ *          (densification_postfix :389 re-creates it before prune_points reads it), so it is not an input;
+ *   a split child has its parent's opacity and scale*(1/1.6) (new_scaling :405), both children share the verdict.
+ * flags uint8[P]: bit0 original kept, bit1 clone kept, bit2 children kept, bit3 split-selected.
+ * counts_host[4] = {kept originals, kept clones, kept children per copy, split-selected S}; rows out =
+ * counts[0] + counts[1] + 2*counts[2].  The call synchronises the stream (the caller sizes the outputs and draws
+ * the 2S x 3 normal samples from it, as the reference's boolean indexing does many times over).
+ * scratch: ws_densify_plan_bytes(P) bytes, kept for ws_densify_gather. */
+size_t ws_densify_plan_bytes(int32_t P);
+int ws_densify_plan(int32_t P, const float *xyz_gradient_accum, const float *denom, const float *opacity,
+                    const float *scaling, float max_grad, float min_opacity, float dense_scale, float big_scale,
+                    int32_t use_screen, float max_screen_size, uint8_t *flags, void *scratch, size_t scratch_bytes,
+                    uint32_t *counts_host, ws_stream_t stream);
+/* One array of the model that travels with the Gaussians: rows of `width` 32-bit words. */
+#define WS_ROW_COPY 0      /* survivors, clones and children copy the source row (f_dc, f_rest, opacity, rotation, _which_object) */
+#define WS_ROW_MOMENT 1    /* survivors copy, clones and children get 0 (exp_avg, exp_avg_sq: :361-362) */
+#define WS_ROW_XYZ 2       /* children: build_rotation(rotation[i]) @ samples[row] + xyz[i] (:401-404), width 3 */
+#define WS_ROW_SCALING 3   /* children: log(exp(scaling[i]) * (1/1.6)) (:405), width 3 */
+typedef struct {
+    const void *src;   /* [P, width] */
+    void *dst;         /* [rows out, width] */
+    int32_t width;
+    int32_t role;      /* WS_ROW_* */
+} ws_row_array;
+/* Writes every array of the model at its new size.  samples float[2S,3]: the reference's
+ * torch.normal(mean=0, std=get_scaling[selected].repeat(2,1)) (:399-400), row r < S for the first child of the
+ * r-th split-selected Gaussian, S + r for the second; rotation float[P,4] raw.  src_row_out int32[rows out] (or NULL):
+ * the source Gaussian of every output row. */
+int ws_densify_gather(int32_t P, const uint8_t *flags, const void *scratch, size_t scratch_bytes,
+                      const uint32_t *counts_host, const float *rotation, const float *samples, int32_t n_arrays,
+                      const ws_row_array *arrays, int32_t *src_row_out, ws_stream_t stream);
+/* GaussianModel.reset_opacity (scene/gaussian_model.py:234-237 + replace_tensor_to_optimizer :295-308):
+ * opacity = inverse_sigmoid(min(sigmoid(opacity), 0.01)) in place, exp_avg = exp_avg_sq = 0 (either may be NULL). */
+int ws_reset_opacity(int32_t P, float *opacity, float *exp_avg, float *exp_avg_sq, ws_stream_t stream);
+
 /* Exchange step of data-parallel training: in-place SUM over ranks of a float buffer that lives in
  * symmetric memory (every rank has mapped every peer's copy), by one kernel on the caller's stream.  Rank r
  * reduces the r-th slice: with multicast_ptr != NULL (NVSwitch multicast address aliasing all copies) through

@@ -172,3 +172,39 @@ def objeval_inputs():
     rows.append(np.zeros_like(hid, dtype=bool))             # 10: empty
     rows.append((hid == 2) | (hid == 3))                    # 11: two heads at once
     return sc, cam, np.stack(rows).astype(bool)
+
+
+# ---- densification: scene/gaussian_model.py:440-458 on a seeded model
+DENSIFY_P = 700
+DENSIFY_SEED = 5
+DENSIFY_TRAIN_ARGS = dict(percent_dense=0.01, position_lr_init=0.00016, position_lr_final=0.0000016,
+                          position_lr_delay_mult=0.01, position_lr_max_steps=30000, feature_lr=0.0025,
+                          opacity_lr=0.05, scaling_lr=0.005, rotation_lr=0.001)   # arguments/__init__.py:74-82
+DENSIFY_CASES = {   # train_vanilla_3dgs.py:106-107: size_threshold = 20 after the first opacity reset, else None
+    "screen": dict(max_grad=0.0002, min_opacity=0.005, extent=2.0, max_screen_size=20),
+    "noscreen": dict(max_grad=0.0002, min_opacity=0.005, extent=2.0, max_screen_size=None),
+}
+
+
+def densify_inputs(P=DENSIFY_P, seed=DENSIFY_SEED, K=3):
+    """Raw parameters, one set of gradients (for the Adam step that fills the moments) and the statistics.
+    Scales straddle percent_dense*extent = 0.02 with a tail beyond 0.1*extent, opacities straddle 0.005,
+    grads straddle 0.0002, some denominators are 0 (0/0 -> NaN -> 0 as :441-442)."""
+    r = np.random.RandomState(seed)
+    f = np.float32
+    inp = {
+        "xyz": r.uniform(-1, 1, (P, 3)).astype(f),
+        "f_dc": r.normal(0, 0.5, (P, 1, 3)).astype(f),
+        "f_rest": r.normal(0, 0.05, (P, K, 3)).astype(f),
+        "opacity": r.normal(-3.0, 2.5, (P, 1)).astype(f),
+        "scaling": (np.log(0.02) + r.normal(0, 1.2, (P, 3))).astype(f),
+        "rotation": r.normal(0, 1, (P, 4)).astype(f),
+        "which_object": r.randint(0, 9, (P, 1)).astype(np.int32),
+    }
+    for n in ("xyz", "f_dc", "f_rest", "opacity", "scaling", "rotation"):
+        inp["g_" + n] = r.normal(0, 1e-3, inp[n].shape).astype(f)
+    denom = r.randint(0, 6, (P, 1)).astype(f)
+    inp["denom"] = denom
+    inp["xyz_gradient_accum"] = (denom * r.uniform(0, 0.0006, (P, 1))).astype(f)
+    inp["max_radii2D"] = r.uniform(0, 40, (P,)).astype(f)
+    return inp

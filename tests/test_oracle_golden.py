@@ -176,3 +176,56 @@ def test_segment_oracle_matches_reference_eval_obj_labels(golden_dir):
     # the merge alone, fed the reference's own renders
     again = segment_oracle.merge({i: (gold["alpha_%d" % i], gold["depth_%d" % i]) for i in renders}, pred.shape)
     assert np.array_equal(again, gold["pred_mask"])
+
+
+DENSIFY_EXACT = ("f_dc", "f_rest", "opacity", "rotation", "which_object")
+
+
+def _densify_before(gold):
+    return {k[len("before/"):]: gold[k] for k in gold.files if k.startswith("before/") and "/step_" not in k}
+
+
+@pytest.mark.parametrize("tag", list(cases.DENSIFY_CASES))
+def test_densify_oracle_matches_reference_class(golden_dir, tag):
+    """oracle/densify_oracle.py against the UNMODIFIED reference GaussianModel.densify_and_prune
+    (tests/golden/make_golden_densify.py): same rows in the same order, moments of new rows zero, statistics reset.
+    Copied rows bit-exact; xyz / scaling of split children pass through exp/log/matmul: 4 ulp."""
+    import densify_oracle
+    gold = _load(golden_dir, "densify")
+    kw = cases.DENSIFY_CASES[tag]
+    inp = cases.densify_inputs()
+    # "before" = the seeded inputs after the one Adam step that fills the moments
+    assert np.array_equal(gold["before/denom"], inp["denom"]) and np.array_equal(gold["before/which_object"], inp["which_object"])
+    st, src, S = densify_oracle.densify_and_prune(_densify_before(gold), gold[tag + "/samples"], kw["max_grad"],
+                                                  kw["min_opacity"], kw["extent"], kw["max_screen_size"],
+                                                  cases.DENSIFY_TRAIN_ARGS["percent_dense"])
+    assert 2 * S == gold[tag + "/samples"].shape[0] and S > 0
+    rows = gold[tag + "/xyz"].shape[0]
+    assert src.shape == (rows,) and rows != inp["xyz"].shape[0]
+    for n in densify_oracle.NAMES:
+        for pre in ("", "m_", "v_"):
+            a, b = st[pre + n], gold["%s/%s%s" % (tag, pre, n)]
+            assert a.shape == b.shape, (pre + n, a.shape, b.shape)
+            if n in DENSIFY_EXACT or pre:
+                assert np.array_equal(a, b), pre + n
+            else:
+                assert np.allclose(a, b, rtol=5e-7, atol=1e-7), (pre + n, np.abs(a - b).max())
+        assert float(gold["%s/step_%s" % (tag, n)]) == float(gold["before/step_" + n]) == 1.0
+    assert np.array_equal(st["which_object"], gold[tag + "/which_object"])
+    for k in ("xyz_gradient_accum", "denom", "max_radii2D"):
+        assert st[k].shape == gold[tag + "/" + k].shape and not st[k].any() and not gold[tag + "/" + k].any()
+    # the structure the fused plan relies on: survivors in order, then clones, then the two child blocks
+    P = inp["xyz"].shape[0]
+    first_new = int(np.argmax(np.diff(src) < 0)) + 1 if (np.diff(src) < 0).any() else rows
+    assert (np.diff(src[:first_new]) > 0).all() and src.max() < P
+    new_rows = ~st["m_xyz"].any(axis=1)
+    assert new_rows[first_new:].all()
+
+
+def test_reset_opacity_oracle_matches_reference_class(golden_dir):
+    import densify_oracle
+    gold = _load(golden_dir, "densify")
+    got = densify_oracle.reset_opacity(gold["before/opacity"])
+    assert np.allclose(got, gold["reset/opacity"], rtol=2e-6, atol=1e-6)
+    assert gold["before/m_opacity"].any() and not gold["reset/m_opacity"].any() and not gold["reset/v_opacity"].any()
+    assert (1 / (1 + np.exp(-got)) <= 0.0100001).all()

@@ -10,7 +10,8 @@ CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libwheatsplat.so")
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 SOURCES = ["ws_api.cu", "ws_preprocess.cu", "ws_radix_sort.cu", "ws_binning.cu", "ws_render_fwd.cu",
-           "ws_render_bwd.cu", "ws_preprocess_bwd.cu", "ws_knn_labels.cu", "ws_loss.cu", "ws_optim.cu", "ws_objeval.cu", "ws_collective.cu"]
+           "ws_render_bwd.cu", "ws_preprocess_bwd.cu", "ws_knn_labels.cu", "ws_loss.cu", "ws_optim.cu", "ws_objeval.cu", "ws_collective.cu",
+           "ws_densify.cu"]
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
          "-Xcompiler", "-fPIC", "-ccbin", "/usr/bin/g++"]
 

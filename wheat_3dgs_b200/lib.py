@@ -19,6 +19,7 @@ SYMBOLS = [
     "ws_knn_dist2", "ws_multi_instance_opt", "ws_sort_bytes", "ws_sort_pairs_u64", "ws_sort_pairs_u32", "ws_set_binning_mode",
     "ws_loss_bytes", "ws_l1_ssim_forward", "ws_l1_ssim_backward", "ws_debug_fetch",
     "ws_adam_step", "ws_densify_stats", "ws_allreduce_sum_f32",
+    "ws_densify_plan_bytes", "ws_densify_plan", "ws_densify_gather", "ws_reset_opacity",
     "ws_objeval_bytes", "ws_objeval_prepare", "ws_objeval_bin", "ws_objeval_render",
     "ws_launch_count", "ws_prof_enable", "ws_prof_read", "ws_prof_stage_name", "ws_debug_count_pairs",
 ]
@@ -53,6 +54,13 @@ class WsGrads(C.Structure):
 
 class WsObjSets(C.Structure):
     _fields_ = [("num_rows", C.c_int32), ("member_start", C.c_void_p), ("member_obj", C.c_void_p)]
+
+
+class WsRowArray(C.Structure):
+    _fields_ = [("src", C.c_void_p), ("dst", C.c_void_p), ("width", C.c_int32), ("role", C.c_int32)]
+
+
+WS_ROW_COPY, WS_ROW_MOMENT, WS_ROW_XYZ, WS_ROW_SCALING = 0, 1, 2, 3
 
 
 class WsAdamGroup(C.Structure):
@@ -133,6 +141,15 @@ def load():
     lib.ws_adam_step.argtypes = [i32, C.POINTER(WsAdamGroup), C.c_double, C.c_double, C.c_double, vp]
     lib.ws_densify_stats.restype = C.c_int
     lib.ws_densify_stats.argtypes = [i32, vp, vp, vp, vp, vp, vp]
+    lib.ws_densify_plan_bytes.restype = sz
+    lib.ws_densify_plan_bytes.argtypes = [i32]
+    lib.ws_densify_plan.restype = C.c_int
+    lib.ws_densify_plan.argtypes = [i32, vp, vp, vp, vp, f32, f32, f32, f32, i32, f32, vp, vp, sz,
+                                    C.POINTER(C.c_uint32), vp]
+    lib.ws_densify_gather.restype = C.c_int
+    lib.ws_densify_gather.argtypes = [i32, vp, vp, sz, C.POINTER(C.c_uint32), vp, vp, i32, C.POINTER(WsRowArray), vp, vp]
+    lib.ws_reset_opacity.restype = C.c_int
+    lib.ws_reset_opacity.argtypes = [i32, vp, vp, vp, vp]
     lib.ws_set_binning_mode.restype = C.c_int
     lib.ws_set_binning_mode.argtypes = [i32]
     lib.ws_sort_pairs_u32.restype = C.c_int
