@@ -51,6 +51,17 @@ class FlashGaussianRasterizationSettings(NamedTuple):
 
 
 _GRAD_BUCKET = None
+_ZERO_PLANES = {}
+
+
+def _zeros(c, H, W, dev):
+    """Read-only zero gradient of an output the loss did not use (autograd hands None with
+    set_materialize_grads(False)); one cached tensor per shape instead of a fill per backward."""
+    key = (c, H, W, dev)
+    z = _ZERO_PLANES.get(key)
+    if z is None:
+        z = _ZERO_PLANES[key] = torch.zeros((c, H, W), dtype=torch.float32, device=dev)
+    return z
 
 
 def set_grad_bucket(bucket):
@@ -90,6 +101,7 @@ class _Rasterize(torch.autograd.Function):
                   rs.sh_degree, rs.campos, rs.prefiltered)
         ctx.flash = flash
         ctx.rs = rs
+        ctx.set_materialize_grads(False)
         if not flash:
             out = _guarded(ops.rasterize_gaussians, common + (rs.debug,), rs.debug, "snapshot_fw.dump", "forward")
             R, color, depth, alpha, radii, geom, binning, image = out
@@ -118,11 +130,11 @@ class _Rasterize(torch.autograd.Function):
         H, W = rs.image_height, rs.image_width
         dev = means3D.device
         if grad_color is None:
-            grad_color = torch.zeros((3, H, W), dtype=torch.float32, device=dev)
+            grad_color = _zeros(3, H, W, dev)
         if grad_depth is None:
-            grad_depth = torch.zeros((1, H, W), dtype=torch.float32, device=dev)
+            grad_depth = _zeros(1, H, W, dev)
         if grad_alpha is None:
-            grad_alpha = torch.zeros((1, H, W), dtype=torch.float32, device=dev)
+            grad_alpha = _zeros(1, H, W, dev)
         tail = (rs.bg, means3D, radii, colors_precomp, scales, rotations, rs.scale_modifier, cov3Ds_precomp,
                 rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy, grad_color, grad_depth, grad_alpha, sh,
                 rs.sh_degree, rs.campos, geom, ctx.num_rendered, binning, image, alpha, rs.debug)
@@ -159,6 +171,7 @@ class _RasterizeRaw(torch.autograd.Function):
         R, color, depth, alpha, radii, geom, binning, image = _guarded(ops.rasterize_gaussians_raw, args, rs.debug,
                                                                        "snapshot_fw.dump", "forward")
         ctx.rs, ctx.num_rendered = rs, R
+        ctx.set_materialize_grads(False)
         ctx.save_for_backward(xyz, features_dc, features_rest, scaling, rotation, radii, geom, binning, image, alpha)
         ctx.mark_non_differentiable(radii)
         return color, radii, depth, alpha
@@ -168,7 +181,7 @@ class _RasterizeRaw(torch.autograd.Function):
         rs = ctx.rs
         xyz, features_dc, features_rest, scaling, rotation, radii, geom, binning, image, alpha = ctx.saved_tensors
         H, W, dev = rs.image_height, rs.image_width, xyz.device
-        z = lambda c: torch.zeros((c, H, W), dtype=torch.float32, device=dev)
+        z = lambda c: _zeros(c, H, W, dev)
         grad_color = z(3) if grad_color is None else grad_color
         grad_depth = z(1) if grad_depth is None else grad_depth
         grad_alpha = z(1) if grad_alpha is None else grad_alpha
