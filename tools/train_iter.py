@@ -9,6 +9,10 @@
              conv2d) -> backward -> the reference's masked-index statistics + torch.optim.Adam
 
     python tools/train_iter.py [iters]        # prints iterations/s of both and the per-part split of ours
+    torchrun --nproc-per-node N ... tools/train_iter.py [iters] ours-raw
+                                              # data parallel: every rank its own view per iteration,
+                                              # gradients written into the symmetric bucket by the backward, summed by
+                                              # libwheatsplat's exchange kernel, then the fused Adam on every rank
 """
 import math
 import os
@@ -22,11 +26,16 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "oracle"))
 import wheat_3dgs_b200  # noqa: E402
-from wheat_3dgs_b200 import loss as wloss, optim as woptim, scene  # noqa: E402
+from wheat_3dgs_b200 import dist as wdist, loss as wloss, optim as woptim, rasterizer as wrast, scene  # noqa: E402
 
 P, W, H, DEG = 1000000, 2048, 1536, 3
 ITERS = int(sys.argv[1]) if len(sys.argv) > 1 else 36
-dev = torch.device("cuda")
+WORLD = int(os.environ.get("WORLD_SIZE", "1"))
+RANK = int(os.environ.get("RANK", "0"))
+if WORLD > 1:
+    torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", "0")))
+    wdist.init_from_env()
+dev = torch.device("cuda", torch.cuda.current_device())
 sc = scene.synthetic_scene(P, seed=0)
 cams = scene.overhead_cameras(W, H)
 t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
@@ -103,10 +112,17 @@ class Trainer:
             import ref as refmod
             self.rr = refmod.RefRasterizer("dgr")
         self.parts = {}
+        self.reduce = None
+        if WORLD > 1:
+            if kind != "ours-raw":
+                raise SystemExit("data-parallel mode runs the ours-raw stack")
+            self.bucket, self.reduce, self.how = wdist.make_bucket(wdist.full_bucket_numel(P, 16), dev)
+            self.n_train = wdist.train_bucket_numel(P, 16)
+            wrast.set_grad_bucket(self.bucket)
 
     def iteration(self, i, ev=None):
         mark = (lambda name: ev.append((name, self._rec()))) if ev is not None else (lambda name: None)
-        c = cd[i % len(cd)]
+        c = cd[(RANK + i * WORLD) % len(cd)]
         gt = gts[i % len(gts)]
         if self.kind == "ours-raw":
             means2D = torch.zeros_like(self.p["xyz"], requires_grad=True)
@@ -124,6 +140,15 @@ class Trainer:
             mark("backward")
             woptim.add_densification_stats(radii, means2D.grad, self.max_radii2D, self.accum, self.denom)
             mark("densify_stats")
+            if self.reduce is not None:
+                # the statistics above are this rank's (summed over ranks only when densification reads them);
+                # the parameter gradients are the bucket's slices, summed in place over all ranks
+                self.reduce(self.n_train)
+                b = self.bucket
+                p["xyz"].grad, p["f_dc"].grad = b[0:3 * P].view(P, 3), b[6 * P:9 * P].view(P, 1, 3)
+                p["f_rest"].grad, p["opacity"].grad = b[9 * P:54 * P].view(P, 15, 3), b[54 * P:55 * P].view(P, 1)
+                p["scaling"].grad, p["rotation"].grad = b[55 * P:58 * P].view(P, 3), b[58 * P:62 * P].view(P, 4)
+                mark("exchange")
             self.opt.step()
             self.opt.zero_grad(set_to_none=True)
             mark("adam")
@@ -167,18 +192,26 @@ class Trainer:
         return e
 
 
+def sync():
+    if WORLD > 1:
+        torch.distributed.barrier()
+    torch.cuda.synchronize()
+
+
 def run(kind):
     tr = Trainer(kind)
     for i in range(3):
         tr.iteration(i)
-    torch.cuda.synchronize()
+    sync()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for i in range(ITERS):
         loss = tr.iteration(3 + i)
     e1.record()
-    torch.cuda.synchronize()
+    sync()
     ms = e0.elapsed_time(e1) / ITERS
+    if WORLD > 1:
+        ms = wdist.max_over_ranks(ms, dev)
     # per-part split (second pass, events between the parts)
     parts = {}
     for i in range(8):
@@ -187,8 +220,14 @@ def run(kind):
         torch.cuda.synchronize()
         for (n0, a), (n1, b) in zip(ev[:-1], ev[1:]):
             parts[n1] = parts.get(n1, 0.0) + a.elapsed_time(b) / 8
-    print("%-9s %.3f ms/iteration = %.1f iterations/s   loss %.5f" % (kind, ms, 1000.0 / ms, float(loss)))
-    print("          " + "  ".join("%s %.3f" % kv for kv in parts.items()))
+    if RANK == 0:
+        if WORLD > 1:
+            print("%-9s %d GPUs (%s): %.3f ms/iteration = %.1f iterations/s = %.1f views/s   loss %.5f"
+                  % (kind, WORLD, tr.how, ms, 1000.0 / ms, WORLD * 1000.0 / ms, float(loss)))
+        else:
+            print("%-9s %.3f ms/iteration = %.1f iterations/s   loss %.5f" % (kind, ms, 1000.0 / ms, float(loss)))
+        print("          " + "  ".join("%s %.3f" % kv for kv in parts.items()))
+    wrast.set_grad_bucket(None)
     del tr
     torch.cuda.empty_cache()
     return ms
@@ -197,6 +236,8 @@ def run(kind):
 if __name__ == "__main__":
     if len(sys.argv) > 2:            # one stack only (profiling target): python tools/train_iter.py 3 ours-raw
         run(sys.argv[2])
+        if WORLD > 1:
+            torch.distributed.destroy_process_group()
         sys.exit(0)
     a = run("ours")
     r = run("ours-raw")
