@@ -278,6 +278,26 @@ int ws_reset_opacity(int32_t P, float *opacity, float *exp_avg, float *exp_avg_s
 int ws_allreduce_sum_f32(int32_t rank, int32_t world, int64_t numel, void *multicast_ptr, void *const *peer_ptrs,
                          int32_t num_ctas, ws_stream_t stream);
 
+/* Exchange + optimiser step of data-parallel training fused into ONE kernel (reduce-scatter, Adam, all-gather):
+ * rank r owns the r-th slice of the flat parameter space [0, numel).  It reads the slice's gradient SUM over ranks
+ * (multimem.ld_reduce from grad_multicast, else peer loads from grad_peers[0..world) in rank order), applies
+ * torch.optim.Adam's step (the element arithmetic of ws_adam_step) with exp_avg / exp_avg_sq indexed like the
+ * parameters (only the slice is touched), and writes the new parameters into every rank's replica
+ * (multimem.st to param_multicast, else stores to param_peers[0..world)).  param_peers is always required (the
+ * local replica is read through param_peers[rank]).  A segment = one param group: elements [begin, end) of the
+ * parameter space, their gradient at grad_offset in the gradient buffer, and the group's lr; segments tile
+ * [0, numel) in order, everything in multiples of 4 floats.  `step` = state["step"] after the increment.
+ * Bracket with the symmetric-memory barrier like ws_allreduce_sum_f32. */
+typedef struct {
+    int64_t begin, end;
+    int64_t grad_offset;
+    double lr;
+} ws_shard_segment;
+int ws_sharded_adam_step(int32_t rank, int32_t world, int64_t numel, int32_t n_segments, const ws_shard_segment *segments,
+                         void *grad_multicast, void *const *grad_peers, void *param_multicast, void *const *param_peers,
+                         float *exp_avg, float *exp_avg_sq, int64_t step, double beta1, double beta2, double eps,
+                         int32_t num_ctas, ws_stream_t stream);
+
 /* The stable LSD radix sort the rasterizer uses (replaces cub::DeviceRadixSort::SortPairs,
  * rasterizer_impl.cu:304-309), exposed for parity tests: sorts (u64 key, u32 value) pairs on
  * key bits [0, end_bit).  Results land in keys_out / vals_out; *_in are clobbered. */

@@ -58,6 +58,66 @@ __global__ void __launch_bounds__(512) allreduce_peers(PeerPtrs peers, int world
     }
 }
 
+
+// ---- reduce-scatter + Adam + all-gather in ONE kernel (sharded optimiser step) ----
+// Parameters are replicated, so after the exchange every rank would run the same Adam step on the same summed
+// gradient (59 P elements, 28 B each).  Here rank r owns the r-th slice of the flat parameter space: it pulls the
+// slice's gradient SUM through the switch (multimem.ld_reduce, or peer loads in rank order), applies Adam with its
+// slice of the moments, and writes the new parameters into every replica (multimem.st, or peer stores).  Link
+// traffic is that of the all-reduce (a slice in, the bucket out for the reduction; the bucket in, a slice out for the
+// broadcast -- of 59 P parameters instead of 62 P gradients), but the summed gradient is never written anywhere, each
+// rank touches 1/W of the optimiser state, and the separate 28 B/element Adam pass over all 59 P elements disappears.
+// Element arithmetic = adam_elem, so parameters are bit-identical to exchange + ws_adam_step.
+constexpr int SA_MAX_SEG = 8;
+struct ShardSeg { long long begin4, goff4; float neg_step; };   // float4 units: first vector, gradient vector of it
+struct ShardAdamParams {
+    ShardSeg seg[SA_MAX_SEG];
+    int n_seg, world, rank;
+    float w1, beta2, w2, eps, bc2_sqrt;
+    const float4 *grad_mc;
+    float4 *param_mc;
+    PeerPtrs grad_peers, param_peers;
+    float4 *m, *v;
+    size_t begin4, end4;
+};
+
+template <bool MC>
+__global__ void __launch_bounds__(512) sharded_adam(const ShardAdamParams P)
+{
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    const float4 *__restrict__ mine = P.param_peers.p[P.rank];
+    for (size_t i = P.begin4 + (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < P.end4; i += stride) {
+        int si = 0;
+#pragma unroll
+        for (int k = 1; k < SA_MAX_SEG; k++)
+            if (k < P.n_seg && (long long)i >= P.seg[k].begin4) si = k;
+        const size_t gi = (size_t)(P.seg[si].goff4 + ((long long)i - P.seg[si].begin4));
+        const float ns = P.seg[si].neg_step;
+        float4 g;
+        if (MC) {
+            g = mc_ld_reduce(P.grad_mc + gi);
+        } else {
+            g = P.grad_peers.p[0][gi];
+            for (int k = 1; k < P.world; k++) {
+                const float4 x = P.grad_peers.p[k][gi];
+                g.x = __fadd_rn(g.x, x.x); g.y = __fadd_rn(g.y, x.y); g.z = __fadd_rn(g.z, x.z); g.w = __fadd_rn(g.w, x.w);
+            }
+        }
+        float4 p = mine[i], m = P.m[i], v = P.v[i];
+        adam_elem(p.x, g.x, m.x, v.x, P.w1, P.beta2, P.w2, P.eps, P.bc2_sqrt, ns);
+        adam_elem(p.y, g.y, m.y, v.y, P.w1, P.beta2, P.w2, P.eps, P.bc2_sqrt, ns);
+        adam_elem(p.z, g.z, m.z, v.z, P.w1, P.beta2, P.w2, P.eps, P.bc2_sqrt, ns);
+        adam_elem(p.w, g.w, m.w, v.w, P.w1, P.beta2, P.w2, P.eps, P.bc2_sqrt, ns);
+        P.m[i] = m;
+        P.v[i] = v;
+        if (MC) {
+            mc_st(P.param_mc + i, p);
+        } else {
+            for (int k = 0; k < P.world; k++) P.param_peers.p[k][i] = p;
+        }
+    }
+}
+
 } // namespace ws
 
 using namespace ws;
@@ -88,6 +148,64 @@ extern "C" int ws_allreduce_sum_f32(int32_t rank, int32_t world, int64_t numel, 
         }
         allreduce_peers<<<ctas, 512, 0, st>>>(pp, world, begin4, end4);
     }
+    WS_LAUNCH_CHECK(st, false);
+    return WS_OK;
+}
+
+extern "C" int ws_sharded_adam_step(int32_t rank, int32_t world, int64_t numel, int32_t n_segments,
+                                    const ws_shard_segment *segments, void *grad_multicast, void *const *grad_peers,
+                                    void *param_multicast, void *const *param_peers, float *exp_avg, float *exp_avg_sq,
+                                    int64_t step, double beta1, double beta2, double eps, int32_t num_ctas,
+                                    ws_stream_t stream)
+{
+    if (world < 1 || world > AR_MAX_WORLD || rank < 0 || rank >= world || numel < 0 || !param_peers || !exp_avg || !exp_avg_sq ||
+        n_segments < 1 || n_segments > SA_MAX_SEG || !segments || step < 1) {
+        set_error("ws_sharded_adam_step: bad arguments (world 1..%d, 1..%d segments, step >= 1)", AR_MAX_WORLD, SA_MAX_SEG);
+        return WS_E_INVALID;
+    }
+    const bool mc = grad_multicast != nullptr && param_multicast != nullptr;
+    if (!mc && !grad_peers) { set_error("ws_sharded_adam_step: neither multicast nor peer gradient pointers"); return WS_E_INVALID; }
+    if (numel % 4 != 0) { set_error("ws_sharded_adam_step: numel must be a multiple of 4"); return WS_E_INVALID; }
+    if (numel == 0) return WS_OK;
+    ShardAdamParams P;
+    P.n_seg = n_segments; P.world = world; P.rank = rank;
+    const double bc1 = 1.0 - pow(beta1, (double)step), bc2 = 1.0 - pow(beta2, (double)step);
+    long long expect = 0;
+    for (int k = 0; k < n_segments; k++) {
+        const ws_shard_segment &s = segments[k];
+        if (s.begin != expect || s.end < s.begin || s.begin % 4 || s.end % 4 || s.grad_offset % 4 || s.grad_offset < 0) {
+            set_error("ws_sharded_adam_step: segment %d: ranges must tile [0, numel) in order, in multiples of 4", k);
+            return WS_E_INVALID;
+        }
+        expect = s.end;
+        P.seg[k].begin4 = s.begin / 4; P.seg[k].goff4 = s.grad_offset / 4;
+        P.seg[k].neg_step = (float)((s.lr / bc1) * -1.0);
+    }
+    if (expect != numel) { set_error("ws_sharded_adam_step: segments end at %lld, numel is %lld", expect, (long long)numel); return WS_E_INVALID; }
+    P.w1 = (float)(1.0 - beta1); P.beta2 = (float)beta2; P.w2 = (float)(1.0 - beta2); P.eps = (float)eps;
+    P.bc2_sqrt = (float)sqrt(bc2);
+    P.grad_mc = (const float4 *)grad_multicast; P.param_mc = (float4 *)param_multicast;
+    for (int k = 0; k < world; k++) {
+        if (!param_peers[k] || ((uintptr_t)param_peers[k] & 15) || (!mc && (!grad_peers[k] || ((uintptr_t)grad_peers[k] & 15)))) {
+            set_error("ws_sharded_adam_step: bad peer pointer %d", k);
+            return WS_E_INVALID;
+        }
+        P.param_peers.p[k] = (float4 *)param_peers[k];
+        P.grad_peers.p[k] = mc ? nullptr : (float4 *)grad_peers[k];
+    }
+    if ((((uintptr_t)exp_avg | (uintptr_t)exp_avg_sq | (uintptr_t)grad_multicast | (uintptr_t)param_multicast) & 15) != 0) {
+        set_error("ws_sharded_adam_step: pointers must be 16-byte aligned");
+        return WS_E_INVALID;
+    }
+    P.m = (float4 *)exp_avg; P.v = (float4 *)exp_avg_sq;
+    const size_t n4 = (size_t)numel / 4, per = (n4 + world - 1) / world;
+    P.begin4 = per * rank < n4 ? per * rank : n4;
+    P.end4 = per * (rank + 1) < n4 ? per * (rank + 1) : n4;
+    if (P.begin4 == P.end4) return WS_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    const int ctas = num_ctas > 0 ? num_ctas : 148;
+    if (mc) sharded_adam<true><<<ctas, 512, 0, st>>>(P);
+    else sharded_adam<false><<<ctas, 512, 0, st>>>(P);
     WS_LAUNCH_CHECK(st, false);
     return WS_OK;
 }

@@ -42,19 +42,7 @@ struct AdamParams {
     float eps;
 };
 
-__device__ __forceinline__ void adam_elem(float &p, float g, float &m, float &v, float w1, float beta2, float w2,
-                                          float eps, float bc2_sqrt, float neg_step)
-{
-    // torch._foreach_lerp_(exp_avgs, grads, 1 - beta1): |w| < 0.5 branch, a + w * (b - a)
-    m = __fmaf_rn(w1, __fsub_rn(g, m), m);
-    // torch._foreach_mul_(exp_avg_sqs, beta2); torch._foreach_addcmul_(exp_avg_sqs, grads, grads, 1 - beta2)
-    v = __fmul_rn(v, beta2);
-    v = __fmaf_rn(w2, __fmul_rn(g, g), v);
-    // _foreach_sqrt, _foreach_div_(bias_correction2_sqrt), _foreach_add_(eps)
-    const float d = __fadd_rn(__fdiv_rn(__fsqrt_rn(v), bc2_sqrt), eps);
-    // torch._foreach_addcdiv_(params, exp_avgs, denom, step_size): p + value * (m / d)
-    p = __fmaf_rn(neg_step, __fdiv_rn(m, d), p);
-}
+// adam_elem: ws_common.cuh (shared with the sharded step of ws_collective.cu)
 
 __global__ void __launch_bounds__(AD_THREADS) adam_groups(const AdamParams P)
 {

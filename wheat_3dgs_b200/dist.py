@@ -199,3 +199,73 @@ def max_over_ranks(value, device):
     t = torch.tensor([float(value)], dtype=torch.float64, device=device)
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
     return float(t.item())
+
+
+class ShardedAdam:
+    """Exchange + optimiser step of data-parallel training as ONE kernel (csrc/ws_collective.cu `sharded_adam`):
+    the replicated parameters live in one symmetric-memory buffer, rank r reduces the r-th slice of the gradient
+    bucket through the switch, applies torch.optim.Adam's step to it with its slice of the moments and stores the
+    new parameters into every replica.  Same numbers as `SymmetricBucket.all_reduce_()` followed by
+    `optim.Adam.step()` on every rank, bit for bit; 1/W of the Adam traffic per rank and no gradient broadcast.
+
+    groups: [{"name", "tensor" (initial value, any device), "lr", "grad_offset" (floats into the bucket)}], in the
+    order they are laid out; every numel and offset a multiple of 4.  `params[name]` are nn.Parameters viewing the
+    symmetric buffer (what the model trains); `bucket` is the SymmetricBucket the backward writes into."""
+
+    def __init__(self, groups, bucket, betas=(0.9, 0.999), eps=1e-8):
+        import ctypes as C
+        import torch.distributed._symmetric_memory as symm
+        from . import lib as _lib
+        from .lib import WsShardSegment
+        if not isinstance(bucket, SymmetricBucket):
+            raise RuntimeError("ShardedAdam needs the gradient bucket in symmetric memory (dist.SymmetricBucket)")
+        self._lib, self._C, self._Seg = _lib, C, WsShardSegment
+        self.bucket, self.betas, self.eps = bucket, betas, float(eps)
+        dev = bucket.tensor.device
+        self.numel = sum(int(g["tensor"].numel()) for g in groups)
+        if any(int(g["tensor"].numel()) % 4 or int(g["grad_offset"]) % 4 for g in groups):
+            raise RuntimeError("ShardedAdam: group sizes and gradient offsets must be multiples of 4 floats")
+        self.flat = symm.empty(self.numel, dtype=torch.float32, device=dev)
+        self.hdl = symm.rendezvous(self.flat, dist.group.WORLD.group_name)
+        self.params, self.groups, off = {}, [], 0
+        for g in groups:
+            n = int(g["tensor"].numel())
+            view = self.flat[off:off + n].view(g["tensor"].shape)
+            view.copy_(g["tensor"].detach().to(dev, torch.float32))
+            self.params[g["name"]] = torch.nn.Parameter(view.requires_grad_(True))
+            self.groups.append({"name": g["name"], "begin": off, "end": off + n, "grad_offset": int(g["grad_offset"]),
+                                "lr": float(g["lr"])})
+            off += n
+        self.exp_avg = torch.zeros(self.numel, dtype=torch.float32, device=dev)
+        self.exp_avg_sq = torch.zeros(self.numel, dtype=torch.float32, device=dev)
+        self.step_count = 0
+        use_mc = bool(bucket.multicast) and bool(self.hdl.multicast_ptr)
+        self.grad_mc = bucket.multicast if use_mc else 0
+        self.param_mc = int(self.hdl.multicast_ptr or 0) if use_mc else 0
+        self.param_peers = (C.c_void_p * bucket.world)(*[int(p) for p in self.hdl.buffer_ptrs])
+        self.num_ctas = int(os.environ.get("WS_SHARDED_ADAM_CTAS", "0"))
+        self.hdl.barrier(channel=0)   # every replica initialised before anyone steps
+
+    def set_lr(self, name, lr):
+        for g in self.groups:
+            if g["name"] == name:
+                g["lr"] = float(lr)
+
+    @torch.no_grad()
+    def step(self):
+        """After every rank's backward has written its gradients into the bucket (same stream)."""
+        C, b = self._C, self.bucket
+        self.step_count += 1
+        segs = (self._Seg * len(self.groups))(*[self._Seg(g["begin"], g["end"], g["grad_offset"], g["lr"])
+                                                for g in self.groups])
+        L = self._lib.load()
+        b.hdl.barrier(channel=0)      # all gradients written, all reads of the old parameters done
+        with torch.cuda.device(self.flat.device):
+            st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+            self._lib.check(L.ws_sharded_adam_step(b.rank, b.world, self.numel, len(self.groups), segs,
+                                                   C.c_void_p(self.grad_mc or None), b.peers,
+                                                   C.c_void_p(self.param_mc or None), self.param_peers,
+                                                   self.exp_avg.data_ptr(), self.exp_avg_sq.data_ptr(), self.step_count,
+                                                   float(self.betas[0]), float(self.betas[1]), self.eps, self.num_ctas, st),
+                            "ws_sharded_adam_step")
+        b.hdl.barrier(channel=1)      # every replica holds the new parameters, the bucket may be rewritten

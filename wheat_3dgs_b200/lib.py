@@ -19,7 +19,7 @@ SYMBOLS = [
     "ws_knn_dist2", "ws_multi_instance_opt", "ws_sort_bytes", "ws_sort_pairs_u64", "ws_sort_pairs_u32", "ws_set_binning_mode",
     "ws_loss_bytes", "ws_l1_ssim_forward", "ws_l1_ssim_backward", "ws_debug_fetch",
     "ws_adam_step", "ws_densify_stats", "ws_allreduce_sum_f32",
-    "ws_densify_plan_bytes", "ws_densify_plan", "ws_densify_gather", "ws_reset_opacity",
+    "ws_sharded_adam_step", "ws_densify_plan_bytes", "ws_densify_plan", "ws_densify_gather", "ws_reset_opacity",
     "ws_objeval_bytes", "ws_objeval_prepare", "ws_objeval_bin", "ws_objeval_render",
     "ws_launch_count", "ws_prof_enable", "ws_prof_read", "ws_prof_stage_name", "ws_debug_count_pairs",
 ]
@@ -54,6 +54,10 @@ class WsGrads(C.Structure):
 
 class WsObjSets(C.Structure):
     _fields_ = [("num_rows", C.c_int32), ("member_start", C.c_void_p), ("member_obj", C.c_void_p)]
+
+
+class WsShardSegment(C.Structure):
+    _fields_ = [("begin", C.c_int64), ("end", C.c_int64), ("grad_offset", C.c_int64), ("lr", C.c_double)]
 
 
 class WsRowArray(C.Structure):
@@ -141,6 +145,9 @@ def load():
     lib.ws_adam_step.argtypes = [i32, C.POINTER(WsAdamGroup), C.c_double, C.c_double, C.c_double, vp]
     lib.ws_densify_stats.restype = C.c_int
     lib.ws_densify_stats.argtypes = [i32, vp, vp, vp, vp, vp, vp]
+    lib.ws_sharded_adam_step.restype = C.c_int
+    lib.ws_sharded_adam_step.argtypes = [i32, i32, i64, i32, C.POINTER(WsShardSegment), vp, C.POINTER(vp), vp,
+                                         C.POINTER(vp), vp, vp, i64, C.c_double, C.c_double, C.c_double, i32, vp]
     lib.ws_densify_plan_bytes.restype = sz
     lib.ws_densify_plan_bytes.argtypes = [i32]
     lib.ws_densify_plan.restype = C.c_int
