@@ -57,6 +57,30 @@ def test_invalid_arguments_are_rejected_without_touching_the_gpu():
     assert L.ws_debug_fetch(b"nope", 1, 16, 16, 0, None, None, None, None, 0, None) == -1
 
 
+def test_densify_and_sharded_step_reject_bad_arguments_on_the_host():
+    """Argument checks of the densification and fused exchange+Adam entry points run before any CUDA call."""
+    L = wlib.load()
+    counts = (C.c_uint32 * 4)()
+    assert L.ws_densify_plan_bytes(1000) > 2 * 3 * 1000 * 4
+    assert L.ws_densify_plan(0, None, None, None, None, 0.0002, 0.005, 0.02, 0.2, 0, 0.0, None, None, 0, counts, None) == 0
+    assert L.ws_densify_plan(-1, None, None, None, None, 0.0002, 0.005, 0.02, 0.2, 0, 0.0, None, None, 0, counts, None) == -1
+    assert L.ws_densify_plan(10, None, None, None, None, 0.0002, 0.005, 0.02, 0.2, 0, 0.0, None, None, 0, counts, None) == -1
+    assert L.ws_densify_plan(10, None, None, None, None, 0.0002, 0.005, 0.02, 0.2, 0, 0.0, None, None, 0, None, None) == -1
+    assert L.ws_densify_gather(0, None, None, 0, None, None, None, 0, None, None, None) == 0
+    assert L.ws_reset_opacity(0, None, None, None, None) == 0
+    assert L.ws_reset_opacity(5, None, None, None, None) == -1
+    seg = (wlib.WsShardSegment * 2)(wlib.WsShardSegment(0, 8, 0, 1e-3), wlib.WsShardSegment(12, 16, 8, 1e-3))   # gap at 8..12
+    peers = (C.c_void_p * 2)(16, 32)
+    m = C.c_void_p(64)
+    assert L.ws_sharded_adam_step(0, 2, 16, 2, seg, None, peers, None, peers, m, m, 1, 0.9, 0.999, 1e-15, 0, None) == -1
+    assert b"tile" in L.ws_last_error()
+    seg[1].begin = 8
+    assert L.ws_sharded_adam_step(0, 2, 16, 2, seg, None, peers, None, peers, m, m, 0, 0.9, 0.999, 1e-15, 0, None) == -1  # step 0
+    assert L.ws_sharded_adam_step(2, 2, 16, 2, seg, None, peers, None, peers, m, m, 1, 0.9, 0.999, 1e-15, 0, None) == -1  # rank
+    assert L.ws_sharded_adam_step(0, 2, 18, 2, seg, None, peers, None, peers, m, m, 1, 0.9, 0.999, 1e-15, 0, None) == -1  # % 4
+    assert L.ws_sharded_adam_step(0, 2, 0, 2, seg, None, peers, None, peers, m, m, 1, 0.9, 0.999, 1e-15, 0, None) == 0
+
+
 def test_both_or_neither_of_an_either_or_pair_is_an_error():
     L = wlib.load()
     v, g = wlib.WsView(), wlib.WsGaussians()

@@ -113,18 +113,29 @@ class Trainer:
             self.rr = refmod.RefRasterizer("dgr")
         self.parts = {}
         self.reduce = None
+        self.sharded = None
         if WORLD > 1:
-            if kind != "ours-raw":
-                raise SystemExit("data-parallel mode runs the ours-raw stack")
-            self.bucket, self.reduce, self.how = wdist.make_bucket(wdist.full_bucket_numel(P, 16), dev)
+            if kind not in ("ours-raw", "ours-fused"):
+                raise SystemExit("data-parallel mode runs the ours-raw / ours-fused stacks")
             self.n_train = wdist.train_bucket_numel(P, 16)
+            if kind == "ours-fused":
+                # exchange + Adam as ONE kernel (dist.ShardedAdam): parameters in symmetric memory, rank r updates slice r
+                sb = wdist.SymmetricBucket(wdist.full_bucket_numel(P, 16), dev)
+                offs = {"xyz": 0, "f_dc": 6 * P, "f_rest": 9 * P, "opacity": 54 * P, "scaling": 55 * P, "rotation": 58 * P}
+                self.sharded = wdist.ShardedAdam([{"name": n, "tensor": self.p[n], "lr": lr, "grad_offset": offs[n]}
+                                                  for n, lr in LRS], sb, eps=1e-15)
+                self.p = self.sharded.params
+                self.bucket, self.reduce = sb.tensor, None
+                self.how = "fused reduce+Adam+broadcast, " + ("multimem" if self.sharded.param_mc else "peers")
+            else:
+                self.bucket, self.reduce, self.how = wdist.make_bucket(wdist.full_bucket_numel(P, 16), dev)
             wrast.set_grad_bucket(self.bucket)
 
     def iteration(self, i, ev=None):
         mark = (lambda name: ev.append((name, self._rec()))) if ev is not None else (lambda name: None)
         c = cd[(RANK + i * WORLD) % len(cd)]
         gt = gts[i % len(gts)]
-        if self.kind == "ours-raw":
+        if self.kind in ("ours-raw", "ours-fused"):
             means2D = torch.zeros_like(self.p["xyz"], requires_grad=True)
             mark("activations")
             rs = self.RS(image_height=H, image_width=W, tanfovx=c["tanfovx"], tanfovy=c["tanfovy"], bg=bg,
@@ -149,6 +160,12 @@ class Trainer:
                 p["f_rest"].grad, p["opacity"].grad = b[9 * P:54 * P].view(P, 15, 3), b[54 * P:55 * P].view(P, 1)
                 p["scaling"].grad, p["rotation"].grad = b[55 * P:58 * P].view(P, 3), b[58 * P:62 * P].view(P, 4)
                 mark("exchange")
+            if self.sharded is not None:
+                self.sharded.step()
+                for q in p.values():
+                    q.grad = None
+                mark("exchange+adam")
+                return loss
             self.opt.step()
             self.opt.zero_grad(set_to_none=True)
             mark("adam")
