@@ -73,8 +73,14 @@ def two_kernels():
 
 t_fused = timed(sh.step)
 t_two = timed(two_kernels)
+sweep = {}
+for ctas in (74, 296, 592):
+    sh.num_ctas = ctas
+    sweep[ctas] = timed(sh.step)
+sh.num_ctas = 0
 if rank == 0:
     print("%d GPUs, P=%d (%s): fused reduce+Adam+broadcast %.3f ms; all-reduce + Adam %.3f ms; bit-identical on all ranks: %s"
           % (world, P, "multimem" if sh.param_mc else "peers", t_fused, t_two, bool(flag.item())), flush=True)
+    print("   CTAs (default 148): " + "  ".join("%d: %.3f ms" % kv for kv in sweep.items()), flush=True)
 torch.distributed.destroy_process_group()
 sys.exit(0 if flag.item() else 1)

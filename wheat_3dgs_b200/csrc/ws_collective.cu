@@ -81,39 +81,52 @@ struct ShardAdamParams {
     size_t begin4, end4;
 };
 
+constexpr int SA_UNROLL = 2;   // independent vectors in flight per thread (the switch round trip is the latency to hide)
 template <bool MC>
 __global__ void __launch_bounds__(512) sharded_adam(const ShardAdamParams P)
 {
     const size_t stride = (size_t)gridDim.x * blockDim.x;
     const float4 *__restrict__ mine = P.param_peers.p[P.rank];
-    for (size_t i = P.begin4 + (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < P.end4; i += stride) {
-        int si = 0;
+    for (size_t i0 = P.begin4 + (size_t)blockIdx.x * blockDim.x + threadIdx.x; i0 < P.end4; i0 += SA_UNROLL * stride) {
+        float4 g[SA_UNROLL], p[SA_UNROLL], m[SA_UNROLL], v[SA_UNROLL];
+        float ns[SA_UNROLL];
 #pragma unroll
-        for (int k = 1; k < SA_MAX_SEG; k++)
-            if (k < P.n_seg && (long long)i >= P.seg[k].begin4) si = k;
-        const size_t gi = (size_t)(P.seg[si].goff4 + ((long long)i - P.seg[si].begin4));
-        const float ns = P.seg[si].neg_step;
-        float4 g;
-        if (MC) {
-            g = mc_ld_reduce(P.grad_mc + gi);
-        } else {
-            g = P.grad_peers.p[0][gi];
-            for (int k = 1; k < P.world; k++) {
-                const float4 x = P.grad_peers.p[k][gi];
-                g.x = __fadd_rn(g.x, x.x); g.y = __fadd_rn(g.y, x.y); g.z = __fadd_rn(g.z, x.z); g.w = __fadd_rn(g.w, x.w);
+        for (int u = 0; u < SA_UNROLL; u++) {
+            const size_t i = i0 + u * stride;
+            if (i >= P.end4) break;
+            int si = 0;
+#pragma unroll
+            for (int k = 1; k < SA_MAX_SEG; k++)
+                if (k < P.n_seg && (long long)i >= P.seg[k].begin4) si = k;
+            const size_t gi = (size_t)(P.seg[si].goff4 + ((long long)i - P.seg[si].begin4));
+            ns[u] = P.seg[si].neg_step;
+            if (MC) {
+                g[u] = mc_ld_reduce(P.grad_mc + gi);
+            } else {
+                g[u] = P.grad_peers.p[0][gi];
+                for (int k = 1; k < P.world; k++) {
+                    const float4 x = P.grad_peers.p[k][gi];
+                    g[u].x = __fadd_rn(g[u].x, x.x); g[u].y = __fadd_rn(g[u].y, x.y);
+                    g[u].z = __fadd_rn(g[u].z, x.z); g[u].w = __fadd_rn(g[u].w, x.w);
+                }
             }
+            p[u] = mine[i]; m[u] = P.m[i]; v[u] = P.v[i];
         }
-        float4 p = mine[i], m = P.m[i], v = P.v[i];
-        adam_elem(p.x, g.x, m.x, v.x, P.w1, P.beta2, P.w2, P.eps, P.bc2_sqrt, ns);
-        adam_elem(p.y, g.y, m.y, v.y, P.w1, P.beta2, P.w2, P.eps, P.bc2_sqrt, ns);
-        adam_elem(p.z, g.z, m.z, v.z, P.w1, P.beta2, P.w2, P.eps, P.bc2_sqrt, ns);
-        adam_elem(p.w, g.w, m.w, v.w, P.w1, P.beta2, P.w2, P.eps, P.bc2_sqrt, ns);
-        P.m[i] = m;
-        P.v[i] = v;
-        if (MC) {
-            mc_st(P.param_mc + i, p);
-        } else {
-            for (int k = 0; k < P.world; k++) P.param_peers.p[k][i] = p;
+#pragma unroll
+        for (int u = 0; u < SA_UNROLL; u++) {
+            const size_t i = i0 + u * stride;
+            if (i >= P.end4) break;
+            adam_elem(p[u].x, g[u].x, m[u].x, v[u].x, P.w1, P.beta2, P.w2, P.eps, P.bc2_sqrt, ns[u]);
+            adam_elem(p[u].y, g[u].y, m[u].y, v[u].y, P.w1, P.beta2, P.w2, P.eps, P.bc2_sqrt, ns[u]);
+            adam_elem(p[u].z, g[u].z, m[u].z, v[u].z, P.w1, P.beta2, P.w2, P.eps, P.bc2_sqrt, ns[u]);
+            adam_elem(p[u].w, g[u].w, m[u].w, v[u].w, P.w1, P.beta2, P.w2, P.eps, P.bc2_sqrt, ns[u]);
+            P.m[i] = m[u];
+            P.v[i] = v[u];
+            if (MC) {
+                mc_st(P.param_mc + i, p[u]);
+            } else {
+                for (int k = 0; k < P.world; k++) P.param_peers.p[k][i] = p[u];
+            }
         }
     }
 }
@@ -203,7 +216,9 @@ extern "C" int ws_sharded_adam_step(int32_t rank, int32_t world, int64_t numel, 
     P.end4 = per * (rank + 1) < n4 ? per * (rank + 1) : n4;
     if (P.begin4 == P.end4) return WS_OK;
     cudaStream_t st = (cudaStream_t)stream;
-    const int ctas = num_ctas > 0 ? num_ctas : 148;
+    // multicast: switch-bound from 74 CTAs up (0.56 ms at 8 GPUs whatever the grid); peer loads want more in flight
+    // (2 GPUs: 148 CTAs 0.43 ms, 592 CTAs 0.38 ms)
+    const int ctas = num_ctas > 0 ? num_ctas : (mc ? 148 : 592);
     if (mc) sharded_adam<true><<<ctas, 512, 0, st>>>(P);
     else sharded_adam<false><<<ctas, 512, 0, st>>>(P);
     WS_LAUNCH_CHECK(st, false);
