@@ -47,7 +47,7 @@ for mode in ("multimem", "peers"):
     mine = sb.tensor.view(torch.int32).sum(dtype=torch.int64)
     lo, hi = mine.clone(), mine.clone()
     dist.all_reduce(lo, op=dist.ReduceOp.MIN); dist.all_reduce(hi, op=dist.ReduceOp.MAX)
-    for ctas in (0, 32, 64):
+    for ctas in (0, 64, 296, 592):
         sb.num_ctas = ctas
         ms = timeit(sb.all_reduce_)
         if rank == 0:
