@@ -104,7 +104,10 @@ __device__ __forceinline__ void cov3d_backward(const float *s, const float *q, c
               4 * z * (dMt[1][1] + dMt[0][0]);
 }
 
-__global__ void __launch_bounds__(WS_PRE_THREADS) preprocess_bwd(const PreBwdParams p)
+#ifndef WS_PB_MINCTAS
+#define WS_PB_MINCTAS 1 // A/B knob: 4 (64 registers, 120 B of spills, 4 CTAs/SM) is 12 us faster on the raw-parameter path and 6 us slower on the standard one
+#endif
+__global__ void __launch_bounds__(WS_PRE_THREADS, WS_PB_MINCTAS) preprocess_bwd(const PreBwdParams p)
 {
     extern __shared__ float4 s_sh4[];
     __shared__ float s_view[16], s_proj[16];
