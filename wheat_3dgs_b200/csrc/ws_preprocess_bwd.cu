@@ -104,10 +104,14 @@ __device__ __forceinline__ void cov3d_backward(const float *s, const float *q, c
               4 * z * (dMt[1][1] + dMt[0][0]);
 }
 
-#ifndef WS_PB_MINCTAS
-#define WS_PB_MINCTAS 1 // A/B knob: 4 (64 registers, 120 B of spills, 4 CTAs/SM) is 12 us faster on the raw-parameter path and 6 us slower on the standard one
+// A/B knob -DWS_PB_MINCTAS=4 (64 registers, 120 B of spills, 4 CTAs/SM instead of 3): 12 us faster on the raw-parameter
+// path, 6 us slower on the standard one -> left off.
+#ifdef WS_PB_MINCTAS
+#define WS_PB_BOUNDS __launch_bounds__(WS_PRE_THREADS, WS_PB_MINCTAS)
+#else
+#define WS_PB_BOUNDS __launch_bounds__(WS_PRE_THREADS)
 #endif
-__global__ void __launch_bounds__(WS_PRE_THREADS, WS_PB_MINCTAS) preprocess_bwd(const PreBwdParams p)
+__global__ void WS_PB_BOUNDS preprocess_bwd(const PreBwdParams p)
 {
     extern __shared__ float4 s_sh4[];
     __shared__ float s_view[16], s_proj[16];
