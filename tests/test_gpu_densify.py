@@ -172,3 +172,58 @@ def test_densify_errors():
     m.xyz_gradient_accum = m.xyz_gradient_accum.cpu()
     with pytest.raises(RuntimeError, match="CUDA tensor"):
         densify.densify_and_prune(m, 0.0002, 0.005, 2.0, None)
+
+
+def test_training_loop_survives_densification_and_opacity_reset():
+    """train_vanilla_3dgs.py:65-112 in miniature on this library only: raw-parameter forward, fused loss, backward,
+    statistics, fused Adam; after a few iterations densify_and_prune changes the number of Gaussians and reset_opacity
+    swaps the opacity parameter; the loop carries on with the new parameters and their optimizer state."""
+    import types as _t
+    from wheat_3dgs_b200 import densify, loss as wloss, optim, scene
+    from wheat_3dgs_b200.rasterizer import GaussianRasterizationSettings, GaussianRasterizer
+    P, W, H = 20000, 200, 150
+    dev = torch.device("cuda")
+    sc = scene.synthetic_scene(P, seed=3, n_heads=20, scale_median=0.01, extent=(0.3, 0.2, 0.12))
+    cam = scene.overhead_cameras(W, H, extent=(0.3, 0.2, 0.12))[17]
+    t = lambda a: torch.from_numpy(np.ascontiguousarray(a, dtype=np.float32)).to(dev)
+    op = np.clip(sc["opacities"], 1e-4, 1 - 1e-4)
+    raw = {"xyz": sc["means3D"], "f_dc": sc["shs"][:, :1], "f_rest": sc["shs"][:, 1:], "opacity": np.log(op / (1 - op)),
+           "scaling": np.log(sc["scales"]), "rotation": sc["rotations"]}
+    m = _t.SimpleNamespace(percent_dense=0.01)
+    groups = []
+    for n, lr in (("xyz", 1.6e-4), ("f_dc", 2.5e-3), ("f_rest", 1.25e-4), ("opacity", 0.05), ("scaling", 5e-3), ("rotation", 1e-3)):
+        p = torch.nn.Parameter(t(raw[n]).requires_grad_(True))
+        setattr(m, ATTR[n], p)
+        groups.append({"params": [p], "lr": lr, "name": n})
+    m.optimizer = optim.Adam(groups, lr=0.0, eps=1e-15)
+    m._which_object = torch.zeros((P, 1), dtype=torch.int32, device=dev)
+    m.xyz_gradient_accum, m.denom = torch.zeros((P, 1), device=dev), torch.zeros((P, 1), device=dev)
+    m.max_radii2D = torch.zeros((P,), device=dev)
+    gt = torch.rand((3, H, W), device=dev)
+    rs = GaussianRasterizationSettings(
+        image_height=H, image_width=W, tanfovx=cam["tanfovx"], tanfovy=cam["tanfovy"], bg=torch.zeros(3, device=dev),
+        scale_modifier=1.0, viewmatrix=t(cam["viewmatrix"]), projmatrix=t(cam["projmatrix"]), sh_degree=3,
+        campos=t(cam["campos"]), prefiltered=False, debug=False)
+
+    def iteration():
+        means2D = torch.zeros_like(m._xyz, requires_grad=True)
+        image, radii, depth, alpha = GaussianRasterizer(rs).forward_raw(m._xyz, means2D, m._features_dc, m._features_rest,
+                                                                        m._opacity, m._scaling, m._rotation)
+        loss = wloss.l1_ssim_loss(image, gt, 0.2)
+        loss.backward()
+        optim.add_densification_stats(radii, means2D.grad, m.max_radii2D, m.xyz_gradient_accum, m.denom)
+        m.optimizer.step()
+        m.optimizer.zero_grad(set_to_none=True)
+        return float(loss.detach())
+
+    first = [iteration() for _ in range(4)]
+    assert all(np.isfinite(first)) and float(m.denom.max()) == 4.0
+    densify.densify_and_prune(m, 1e-7, 0.005, 0.36, None)   # low threshold: every seen Gaussian is cloned or split
+    P2 = m._xyz.shape[0]
+    assert P2 > P and m._features_rest.shape == (P2, 15, 3) and m._which_object.shape == (P2, 1)
+    assert m.optimizer.state[m._xyz]["exp_avg"].shape == (P2, 3) and float(m.optimizer.state[m._xyz]["step"]) == 4.0
+    densify.reset_opacity(m)
+    assert float(torch.sigmoid(m._opacity).max()) <= 0.0100001
+    after = [iteration() for _ in range(3)]
+    assert all(np.isfinite(after)) and float(m.optimizer.state[m._xyz]["step"]) == 7.0
+    assert m.denom.shape == (P2, 1) and float(m.denom.max()) == 3.0
