@@ -32,6 +32,7 @@ struct AdamGroupDev {
     long long chunk_begin;     // first chunk of this group in the flat chunk space
     float neg_step_size;       // -(lr / (1 - beta1^step))
     float bc2_sqrt;            // sqrt(1 - beta2^step)
+    int grad_vec;              // 1: grad is 16-byte aligned (float4 loads); 0: only 4-byte aligned (scalar loads)
 };
 struct AdamParams {
     AdamGroupDev g[AD_MAX_GROUPS];
@@ -56,7 +57,11 @@ __global__ void __launch_bounds__(AD_THREADS) adam_groups(const AdamParams P)
         if (base >= G.numel) continue;
         if (base + 4 <= G.numel) {
             float4 p = *reinterpret_cast<const float4 *>(G.param + base);
-            const float4 g = __ldcs(reinterpret_cast<const float4 *>(G.grad + base));
+            // the gradients are slices of ONE flat bucket (ops._backward): at offsets 3P, 6P, ... they are 16-byte
+            // aligned only when P is a multiple of 4, which it is not after most densifications
+            const float4 g = G.grad_vec ? __ldcs(reinterpret_cast<const float4 *>(G.grad + base))
+                                        : make_float4(__ldcs(G.grad + base), __ldcs(G.grad + base + 1),
+                                                      __ldcs(G.grad + base + 2), __ldcs(G.grad + base + 3));
             float4 m = *reinterpret_cast<const float4 *>(G.exp_avg + base);
             float4 v = *reinterpret_cast<const float4 *>(G.exp_avg_sq + base);
             adam_elem(p.x, g.x, m.x, v.x, P.w1, P.beta2, P.w2, P.eps, G.bc2_sqrt, G.neg_step_size);
@@ -113,13 +118,14 @@ extern "C" int ws_adam_step(int32_t n_groups, const ws_adam_group *groups, doubl
             set_error("ws_adam_step: group %d has a NULL tensor", k);
             return WS_E_INVALID;
         }
-        if ((((uintptr_t)g.param | (uintptr_t)g.grad | (uintptr_t)g.exp_avg | (uintptr_t)g.exp_avg_sq) & 15) != 0) {
-            set_error("ws_adam_step: group %d: tensors must be 16-byte aligned", k);
+        if ((((uintptr_t)g.param | (uintptr_t)g.exp_avg | (uintptr_t)g.exp_avg_sq) & 15) != 0 || ((uintptr_t)g.grad & 3) != 0) {
+            set_error("ws_adam_step: group %d: param / exp_avg / exp_avg_sq must be 16-byte aligned, grad 4-byte aligned", k);
             return WS_E_INVALID;
         }
         AdamGroupDev &d = P.g[P.n_groups++];
         d.param = g.param; d.grad = g.grad; d.exp_avg = g.exp_avg; d.exp_avg_sq = g.exp_avg_sq;
         d.numel = g.numel; d.chunk_begin = chunks;
+        d.grad_vec = ((uintptr_t)g.grad & 15) == 0 ? 1 : 0;
         // torch/optim/adam.py (_multi_tensor_adam): Python doubles, cast to float at the kernel boundary
         const double bc1 = 1.0 - pow(beta1, (double)g.step);
         const double bc2 = 1.0 - pow(beta2, (double)g.step);

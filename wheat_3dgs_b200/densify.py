@@ -90,6 +90,8 @@ def densify_and_prune(model, max_grad, min_opacity, extent, max_screen_size, ret
         if src.element_size() not in (4, 8):
             raise RuntimeError("densify: rows must be made of 4- or 8-byte elements")
         dst = torch.empty((rows,) + tuple(src.shape[1:]), dtype=src.dtype, device=dev)
+        if w == 0:   # zero-width rows (features_rest [P,0,3] at max_sh_degree 0): nothing to move
+            return dst
         table.append(WsRowArray(src.data_ptr(), dst.data_ptr(), w * src.element_size() // 4, role))
         keep.append(src)
         return dst

@@ -168,7 +168,10 @@ def allreduce_votes(used_count, async_op=False):
 
 
 def allreduce_densify_stats(xyz_gradient_accum, denom, max_radii2D):
-    """Densification statistics (scene/gaussian_model.py:461-463): SUM, SUM, MAX."""
+    """Densification statistics (scene/gaussian_model.py:461-463): SUM, SUM, MAX, IN PLACE on every rank.
+    The statistics are cumulative over a densification interval, so call this EXACTLY ONCE per interval, immediately
+    before densify_and_prune reads them (which then resets them): a second call would add the already summed values
+    again (x world_size)."""
     if world_size() == 1:
         return
     dist.all_reduce(xyz_gradient_accum, op=dist.ReduceOp.SUM)
@@ -210,7 +213,10 @@ class ShardedAdam:
 
     groups: [{"name", "tensor" (initial value, any device), "lr", "grad_offset" (floats into the bucket)}], in the
     order they are laid out; every numel and offset a multiple of 4.  `params[name]` are nn.Parameters viewing the
-    symmetric buffer (what the model trains); `bucket` is the SymmetricBucket the backward writes into."""
+    symmetric buffer (what the model trains); `bucket` is the SymmetricBucket the backward writes into.
+
+    The flat buffers have a fixed size: after densify_and_prune (a new P) build a NEW ShardedAdam (and bucket) from
+    the new tensors with `rebuild()`; P must be a multiple of 4 (pad the model with culled rows otherwise)."""
 
     def __init__(self, groups, bucket, betas=(0.9, 0.999), eps=1e-8):
         import ctypes as C
@@ -245,6 +251,19 @@ class ShardedAdam:
         self.param_peers = (C.c_void_p * bucket.world)(*[int(p) for p in self.hdl.buffer_ptrs])
         self.num_ctas = int(os.environ.get("WS_SHARDED_ADAM_CTAS", "0"))
         self.hdl.barrier(channel=0)   # every replica initialised before anyone steps
+
+    def rebuild(self, groups, bucket, moments=None):
+        """A new ShardedAdam for the post-densification tensors; `moments` = {name: (exp_avg, exp_avg_sq)} rows to
+        carry over (the reference keeps the moments of surviving rows, scene/gaussian_model.py:296-345)."""
+        new = ShardedAdam(groups, bucket, betas=self.betas, eps=self.eps)
+        new.step_count = self.step_count
+        if moments:
+            for g in new.groups:
+                if g["name"] in moments:
+                    m, v = moments[g["name"]]
+                    new.exp_avg[g["begin"]:g["end"]].copy_(m.reshape(-1))
+                    new.exp_avg_sq[g["begin"]:g["end"]].copy_(v.reshape(-1))
+        return new
 
     def set_lr(self, name, lr):
         for g in self.groups:

@@ -79,6 +79,30 @@ _BIN_POOL = {}   # (device, stream) -> [uint8 base tensors]
 _USE_COUNT = getattr(torch._C, "_storage_Use_Count", None)
 
 
+def _calibrate_use_count():
+    """The pool below decides reuse from torch's private storage use count.  Check, once at import, that the
+    count behaves as `_in_use` assumes (2 for a tensor nobody else references: the tensor + the temporary
+    untyped_storage() wrapper; 3 with one view alive); if a torch version counts differently the pool is
+    switched off and every call allocates (slower, never wrong)."""
+    global _USE_COUNT
+    if _USE_COUNT is None:
+        return
+    try:
+        base = torch.empty((64,), dtype=torch.uint8)
+        alone = _USE_COUNT(base.untyped_storage()._cdata)
+        view = base.narrow(0, 0, 8)
+        shared = _USE_COUNT(base.untyped_storage()._cdata)
+        del view
+        again = _USE_COUNT(base.untyped_storage()._cdata)
+        if not (alone == 2 and shared == 3 and again == 2):
+            _USE_COUNT = None
+    except Exception:  # noqa: BLE001 - private API gone or changed
+        _USE_COUNT = None
+
+
+_calibrate_use_count()
+
+
 def _in_use(base):
     # references to the storage besides the pool's tensor and the temporary made here: views handed out earlier that
     # are still alive in Python or saved in an autograd graph

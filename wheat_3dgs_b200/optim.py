@@ -53,7 +53,7 @@ class Adam(torch.optim.Optimizer):
                 loss = closure()
         L = _lib.load()
         batches = {}   # (beta1, beta2, eps, device) -> [WsAdamGroup]
-        keep = []
+        keep, bump = [], []
         for group in self.param_groups:
             beta1, beta2 = group["betas"]
             for p in group["params"]:
@@ -72,7 +72,6 @@ class Adam(torch.optim.Optimizer):
                     st["exp_avg_sq"] = torch.zeros_like(p, memory_format=torch.preserve_format)
                 if "step" not in st:
                     st["step"] = torch.tensor(0.0, dtype=torch.float32)
-                st["step"] += 1
                 g = p.grad
                 if g.dtype != torch.float32 or not g.is_contiguous():
                     g = g.to(torch.float32).contiguous()
@@ -80,16 +79,23 @@ class Adam(torch.optim.Optimizer):
                 if not (m.is_contiguous() and v.is_contiguous()):
                     m = st["exp_avg"] = m.contiguous()
                     v = st["exp_avg_sq"] = v.contiguous()
+                if (p.data_ptr() | m.data_ptr() | v.data_ptr()) & 15:
+                    raise RuntimeError("wheat_3dgs_b200.optim.Adam: parameters and moments must be 16-byte aligned")
+                # gradients may be 4-byte aligned only: they are slices of the flat bucket ops._backward() fills, at
+                # offsets 3P, 6P, ... (the kernel then loads them with scalar instructions)
                 keep.append(g)
+                bump.append(st)
                 batches.setdefault((float(beta1), float(beta2), float(group["eps"]), p.device), []).append(
                     WsAdamGroup(p.data_ptr(), g.data_ptr(), m.data_ptr(), v.data_ptr(), p.numel(),
-                                float(group["lr"]), int(st["step"].item())))
+                                float(group["lr"]), int(st["step"].item()) + 1))
         for (beta1, beta2, eps, dev), groups in batches.items():
             with torch.cuda.device(dev):
                 for i in range(0, len(groups), _MAX_GROUPS):
                     chunk = groups[i:i + _MAX_GROUPS]
                     arr = (WsAdamGroup * len(chunk))(*chunk)
                     _lib.check(L.ws_adam_step(len(chunk), arr, beta1, beta2, eps, _stream()), "ws_adam_step")
+        for st in bump:   # only once every launch went through: a raised error leaves the step counts untouched
+            st["step"] += 1
         return loss
 
 

@@ -72,6 +72,21 @@ def set_grad_bucket(bucket):
     _GRAD_BUCKET = bucket
 
 
+def _check_bucket_free(leaf):
+    """With a gradient bucket set, the gradients autograd hands to the leaves ARE slices of the bucket.  A second
+    backward before the first one's .grad tensors are dropped would overwrite them in place and then be ADDED to
+    itself by AccumulateGrad (2 x new instead of old + new): one backward per bucket per step."""
+    g = getattr(leaf, "grad", None)
+    b = _GRAD_BUCKET
+    if g is None or b is None or g.device != b.device:
+        return
+    lo, hi = b.data_ptr(), b.data_ptr() + b.numel() * b.element_size()
+    if lo <= g.data_ptr() < hi:
+        raise RuntimeError("set_grad_bucket: the previous backward's gradients still alias the bucket; drop them "
+                           "(optimizer.zero_grad(set_to_none=True) / p.grad = None) before the next backward -- "
+                           "gradient accumulation over several backwards needs set_grad_bucket(None)")
+
+
 def _snapshot(args, path):
     """debug=True behaviour of the reference: CPU copy of the inputs dumped when the call throws
     (DGR __init__.py:83-90,135-142)."""
@@ -141,6 +156,7 @@ class _Rasterize(torch.autograd.Function):
         if not ctx.flash:
             fn = ops.rasterize_gaussians_backward
             if _GRAD_BUCKET is not None:
+                _check_bucket_free(means3D)
                 fn = lambda *a: ops.rasterize_gaussians_backward(*a, _bucket=_GRAD_BUCKET)  # noqa: E731
             g = _guarded(fn, tail, rs.debug, "snapshot_bw.dump", "backward")
         else:
@@ -190,6 +206,7 @@ class _RasterizeRaw(torch.autograd.Function):
                 ctx.num_rendered, binning, image, alpha, rs.debug)
         fn = ops.rasterize_gaussians_raw_backward
         if _GRAD_BUCKET is not None:
+            _check_bucket_free(xyz)
             fn = lambda *a: ops.rasterize_gaussians_raw_backward(*a, _bucket=_GRAD_BUCKET)  # noqa: E731
         g2d, gop, gxyz, gdc, grest, gsc, grot = _guarded(fn, args, rs.debug, "snapshot_bw.dump", "backward")
         return gxyz, g2d, gdc, grest, gop, gsc, grot, None
