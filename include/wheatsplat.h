@@ -206,7 +206,8 @@ int ws_objeval_render(const ws_view *view, const ws_objsets *sets, void *binning
  * ws_adam_step = torch.optim.Adam(...).step() as GaussianModel.training_setup configures it
  * (scene/gaussian_model.py:167-186; called at train_vanilla_3dgs.py:110-112): betas/eps shared, one
  * learning rate and step count per parameter group, no weight decay, no amsgrad.  All groups (at most 8)
- * are updated by ONE kernel launch, in place.  Tensors are contiguous float, 16-byte aligned. */
+ * are updated by ONE kernel launch, in place.  Tensors are contiguous float; param / exp_avg / exp_avg_sq
+ * 16-byte aligned, grad 4-byte aligned (16-byte aligned gradients are loaded as vectors). */
 typedef struct ws_adam_group {
     float *param;        /* [numel] updated in place */
     const float *grad;   /* [numel] */
@@ -348,6 +349,12 @@ const char *ws_prof_stage_name(int32_t stage);
  * counts is device uint64[2], zeroed by the call. */
 int ws_debug_count_pairs(int32_t width, int32_t height, void *binning, void *image, int64_t num_rendered,
                          uint64_t *counts, ws_stream_t stream);
+
+/* FP32 issue-rate probe (bench.py's measured roofline denominator for the blend kernels): `ctas` CTAs of 256
+ * threads each run iters x 32 dependent-chain FMAs (8 independent chains, three register operands); packed != 0
+ * issues fma.rn.f32x2 (FFMA2) as the blend kernels do, else scalar FFMA.  out: device float[ctas * 256].
+ * Returns the number of floating-point operations issued (or a negative status). */
+int64_t ws_debug_fma_peak(int32_t packed, int32_t iters, int32_t ctas, float *out, ws_stream_t stream);
 
 #ifdef __cplusplus
 }

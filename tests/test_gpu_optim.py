@@ -144,3 +144,67 @@ def test_optim_rejects_cpu_tensors_and_handles_empty():
                                        torch.zeros(3, 1), torch.zeros(3, 1))
     with pytest.raises(ValueError):
         woptim.Adam([e], lr=0.1, amsgrad=True)
+
+
+def test_adam_takes_gradient_slices_of_the_flat_bucket_at_odd_P():
+    """P is arbitrary after densify_and_prune; the gradients the raw entry hands to the leaves are slices of ONE flat
+    allocation at offsets 3P, 6P, ... (ops._backward), 16-byte aligned only when P % 4 == 0.  The fused step must
+    take them and agree with torch.optim.Adam bit for bit."""
+    from wheat_3dgs_b200 import optim as woptim
+    for P in (20001, 20002, 20003):
+        gen = torch.Generator(device="cuda").manual_seed(P)
+        shapes = {"xyz": (P, 3), "f_dc": (P, 1, 3), "f_rest": (P, 15, 3), "opacity": (P, 1), "scaling": (P, 3),
+                  "rotation": (P, 4)}
+        init = {k: torch.randn(s, device="cuda", generator=gen) for k, s in shapes.items()}
+        mine = {k: torch.nn.Parameter(v.clone()) for k, v in init.items()}
+        ref = {k: torch.nn.Parameter(v.clone()) for k, v in init.items()}
+        lrs = dict(xyz=0.00016, f_dc=0.0025, f_rest=0.000125, opacity=0.05, scaling=0.005, rotation=0.001)
+        o1 = woptim.Adam([{"params": [mine[k]], "lr": lrs[k], "name": k} for k in shapes], lr=0.0, eps=1e-15)
+        o2 = torch.optim.Adam([{"params": [ref[k]], "lr": lrs[k], "name": k} for k in shapes], lr=0.0, eps=1e-15)
+        offs = {"xyz": 0, "f_dc": 6 * P, "f_rest": 9 * P, "opacity": 54 * P, "scaling": 55 * P, "rotation": 58 * P}
+        misaligned = 0
+        for _ in range(2):
+            bucket = torch.randn(71 * P, device="cuda", generator=gen) * 1e-3
+            for k, s in shapes.items():
+                g = bucket[offs[k]:offs[k] + mine[k].numel()].view(s)
+                misaligned += int(g.data_ptr() % 16 != 0)
+                mine[k].grad = g
+                ref[k].grad = g.clone()
+            o1.step()
+            o2.step()
+        assert misaligned > 0
+        for k in shapes:
+            assert torch.equal(mine[k].detach(), ref[k].detach()), (P, k)
+            assert int(o1.state[mine[k]]["step"].item()) == 2
+
+
+def test_raw_training_loop_at_odd_P_and_bucket_guard():
+    """forward_raw + optim.Adam at P % 4 != 0 (the advertised loop right after a densification), and the guard against a
+    second backward into a bucket whose slices are still some parameter's .grad."""
+    import wheat_3dgs_b200
+    from wheat_3dgs_b200 import rasterizer as rz, scene, train
+    P, W, H = 20001, 160, 120
+    sc = scene.synthetic_scene(P, seed=0, scale_median=0.004)
+    cam = scene.overhead_cameras(W, H)[17]
+    dev = torch.device("cuda")
+    t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+    cd = dict(cam, viewmatrix=t(cam["viewmatrix"]), projmatrix=t(cam["projmatrix"]), campos=t(cam["campos"]))
+    tr = train.Trainer(train.raw_params_from_scene(sc, dev), 3, dev)
+    gt = torch.rand(3, H, W, device=dev)
+    bg = torch.zeros(3, device=dev)
+    before = tr.p["xyz"].detach().clone()
+    l0 = float(tr.iteration(cd, gt, bg))
+    l1 = float(tr.iteration(cd, gt, bg))
+    assert np.isfinite(l0) and np.isfinite(l1) and not torch.equal(before, tr.p["xyz"].detach())
+    # bucket guard
+    bucket = torch.empty(71 * P, device=dev)
+    rz.set_grad_bucket(bucket)
+    try:
+        m2d = torch.zeros_like(tr.p["xyz"], requires_grad=True)
+        img = tr.render(cd, bg, m2d)[0]
+        img.sum().backward()
+        img2 = tr.render(cd, bg, m2d)[0]
+        with pytest.raises(RuntimeError, match="alias the bucket"):
+            img2.sum().backward()
+    finally:
+        rz.set_grad_bucket(None)

@@ -363,6 +363,60 @@ __global__ void __launch_bounds__(256) count_pairs(int W, int H, const uint2 *__
 }
 } // namespace ws
 
+namespace ws {
+// FP32 issue-rate probe for the blend kernels' roofline (bench.py): every thread runs 8 independent dependent-FMA
+// chains, three distinct register operands per FMA as in the blend loops.  PACKED: fma.rn.f32x2 (FFMA2, what the
+// blend kernels issue); otherwise scalar FFMA.
+template <bool PACKED>
+__global__ void __launch_bounds__(256) fma_peak(int iters, float b0, float c0, float *__restrict__ out)
+{
+    const float t = (float)threadIdx.x * 1e-3f;
+    if (PACKED) {
+        f2 a[8];
+#pragma unroll
+        for (int k = 0; k < 8; k++) a[k] = pk2(t + (float)k, t - (float)k);
+        const f2 b = pk2(b0, b0 * 0.999f), c = pk2(c0, c0 * 1.001f);
+        for (int i = 0; i < iters; i++) {
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+#pragma unroll
+                for (int k = 0; k < 8; k++) a[k] = fma2(a[k], b, c);
+            }
+        }
+        float s = 0.f;
+#pragma unroll
+        for (int k = 0; k < 8; k++) s += lo2(a[k]) + hi2(a[k]);
+        out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+    } else {
+        float a[8];
+#pragma unroll
+        for (int k = 0; k < 8; k++) a[k] = t + (float)k;
+        for (int i = 0; i < iters; i++) {
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+#pragma unroll
+                for (int k = 0; k < 8; k++) a[k] = __fmaf_rn(a[k], b0, c0);
+            }
+        }
+        float s = 0.f;
+#pragma unroll
+        for (int k = 0; k < 8; k++) s += a[k];
+        out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+    }
+}
+} // namespace ws
+
+extern "C" int64_t ws_debug_fma_peak(int32_t packed, int32_t iters, int32_t ctas, float *out, ws_stream_t stream)
+{
+    if (iters < 1 || ctas < 1 || !out) { set_error("ws_debug_fma_peak: bad arguments"); return WS_E_INVALID; }
+    cudaStream_t st = (cudaStream_t)stream;
+    if (packed) ws::fma_peak<true><<<ctas, 256, 0, st>>>(iters, 0.9999f, 1e-4f, out);
+    else ws::fma_peak<false><<<ctas, 256, 0, st>>>(iters, 0.9999f, 1e-4f, out);
+    WS_LAUNCH_CHECK(st, false);
+    // flops issued: threads x iters x 32 FMAs x 2 (x 2 when packed)
+    return (int64_t)ctas * 256 * (int64_t)iters * 32 * 2 * (packed ? 2 : 1);
+}
+
 extern "C" int ws_debug_count_pairs(int32_t width, int32_t height, void *binning, void *image, int64_t num_rendered,
                                     uint64_t *counts, ws_stream_t stream)
 {

@@ -22,6 +22,7 @@ SYMBOLS = [
     "ws_sharded_adam_step", "ws_densify_plan_bytes", "ws_densify_plan", "ws_densify_gather", "ws_reset_opacity",
     "ws_objeval_bytes", "ws_objeval_prepare", "ws_objeval_bin", "ws_objeval_render",
     "ws_launch_count", "ws_prof_enable", "ws_prof_read", "ws_prof_stage_name", "ws_debug_count_pairs",
+    "ws_debug_fma_peak",
 ]
 WS_PROF_NSTAGES = 8
 
@@ -171,6 +172,8 @@ def load():
     lib.ws_prof_stage_name.argtypes = [i32]
     lib.ws_debug_count_pairs.restype = C.c_int
     lib.ws_debug_count_pairs.argtypes = [i32, i32, vp, vp, i64, vp, vp]
+    lib.ws_debug_fma_peak.restype = i64
+    lib.ws_debug_fma_peak.argtypes = [i32, i32, i32, vp, vp]
     if lib.ws_abi_version() != WS_ABI_VERSION:
         raise ImportError("libwheatsplat.so ABI %d != expected %d" % (lib.ws_abi_version(), WS_ABI_VERSION))
     _lib = lib

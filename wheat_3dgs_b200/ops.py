@@ -452,3 +452,22 @@ def count_pairs(W, H, R, binning, image):
                    "ws_debug_count_pairs")
     c = counts.cpu().tolist()
     return int(c[0]), int(c[1])
+
+
+def fma_peak(packed, device=None, iters=4096, ctas=148 * 8, repeats=5):
+    """Measured FP32 FMA throughput in TFLOP/s (best of `repeats`, CUDA events on the current stream): the blend
+    kernels' roofline denominator.  packed=True issues FFMA2 (fma.rn.f32x2), False scalar FFMA."""
+    L = _lib.load()
+    dev = torch.device("cuda", torch.cuda.current_device()) if device is None else device
+    out = torch.empty((ctas * 256,), dtype=torch.float32, device=dev)
+    best = 0.0
+    with torch.cuda.device(dev):
+        for _ in range(repeats + 1):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            flops = _lib.check(L.ws_debug_fma_peak(1 if packed else 0, iters, ctas, out.data_ptr(), _stream()),
+                               "ws_debug_fma_peak")
+            e1.record()
+            e1.synchronize()
+            best = max(best, flops / (e0.elapsed_time(e1) * 1e-3) / 1e12)
+    return best

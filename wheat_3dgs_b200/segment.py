@@ -137,3 +137,146 @@ def eval_obj_labels(all_obj_labels, viewpoint_cam, gaussians, pipe, background):
     return eval_obj_labels_tensors(all_obj_labels, rs, gaussians.get_xyz, gaussians.get_opacity,
                                    shs=gaussians.get_features, scales=gaussians.get_scaling,
                                    rotations=gaussians.get_rotation)
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# run_3d_seg.py on the device: per-mask label votes, find_match over the other views, the growing loop
+# ---------------------------------------------------------------------------------------------------------------
+_E = torch.Tensor([])
+
+
+def best_mask_iou(pred, ids, area):
+    """find_match's inner search (run_3d_seg.py:134-157) for one view: `pred` bool [H,W] = alpha > 0.5, `ids` int64
+    [H,W] instance-id image, `area` = bincount(ids).  Returns float64 [2] = (max IoU over the masks k >= 1, lowest
+    k attaining it); (0, 0) when nothing overlaps."""
+    inter = torch.bincount(ids[pred], minlength=area.numel()).to(torch.float64)
+    union = area.to(torch.float64) + pred.sum().to(torch.float64) - inter
+    iou = torch.where(union > 0, inter / union.clamp(min=1.0), torch.zeros_like(union))
+    iou[0] = 0.0                                   # id 0 is "no mask"
+    m = iou.max()
+    first = torch.nonzero(iou == m)[0, 0]          # lowest index among equals (the reference scans with a strict >)
+    first = torch.where(m > 0, first, torch.zeros_like(first))
+    return torch.stack([m, first.to(torch.float64)])
+
+
+class HeadSegmenter:
+    """The 3D-segmentation loop of run_3d_seg.py:243-315 for ONE seed mask at a time, everything on the device.
+
+    Inputs stand in for what the script reads from disk: `g` = the post-activation Gaussian tensors
+    (means3D, opacities, shs, scales, rotations), `cams` = camera dicts with device matrices, `id_masks[v]` =
+    float32 [H,W] instance-id image of view v (0 = no mask, k = the k-th YOLO/SAM mask of that view: the
+    reference's per-mask PNGs of one view do not overlap in the synthetic workload, so one id image holds them
+    all).  `pts_filter` = run_3d_seg.py:208 (Gaussians below the mean height never join an object).
+
+      seed_counts(v, k)        opt_label_w_seg([view], [mask], pts_filter)      :263 -> :74-105
+      labels_of(counts)        counts_to_obj_labels -> row 1                    :264-268 -> :107-114
+      find_match(views, used)  find_match over the given views                  :275 -> :116-173
+      segment_seed(v, k)       the whole loop for one seed, up to 99 rounds     :263-315
+
+    find_match's host side (alpha > 0.5, bbox, box overlap, per-mask IoU in numpy, :130-157) runs as one
+    bincount per view on the device: IoU_k = |pred & mask_k| / (|pred| + |mask_k| - |pred & mask_k|) for every
+    mask of the view at once.  The YOLO boxes are the masks' bounding boxes, so a mask whose box misses the
+    prediction's has IoU 0 and can never win `iou > max_iou` (max_iou starts at 0.0): the box filter only saves
+    work and is dropped.  Ties keep the lowest mask index, as the reference's strict `>` scan does."""
+
+    def __init__(self, g, cams, id_masks, bg, sh_degree, iou_threshold=0.6, pts_filter=None):
+        self.g, self.cams, self.bg, self.deg = g, cams, bg, int(sh_degree)
+        self.id_masks = id_masks
+        self.iou_threshold = float(iou_threshold)
+        self.P = int(g["means3D"].shape[0])
+        self.dev = g["means3D"].device
+        if pts_filter is None:   # run_3d_seg.py:206-208
+            z = g["means3D"][:, 2]
+            pts_filter = z < z.mean()
+        self.pts_filter = pts_filter
+        self._ids = {}     # view -> (int64 id image, per-id pixel counts)
+        self.renders = 0   # rasterizer forwards issued (the unit the reference's cost is counted in)
+
+    # -- votes
+    def _flash(self, v, mask, num_obj, used_out=None):
+        c = self.cams[v]
+        g = self.g
+        self.renders += 1
+        return _ops.flash_rasterize_gaussians(mask, None, self.bg, g["means3D"], _E, g["opacities"], g["scales"],
+                                              g["rotations"], 1.0, _E, c["viewmatrix"], c["projmatrix"], c["tanfovx"],
+                                              c["tanfovy"], c["image_height"], c["image_width"], g["shs"], self.deg,
+                                              c["campos"], False, int(num_obj), False, used_count_out=used_out)
+
+    def view_counts(self, v, num_obj=None):
+        """ONE multi-label vote pass over all masks of view v: used_count [num_obj+1, P]."""
+        m = self.id_masks[v]
+        if num_obj is None:
+            num_obj = int(m.max().item())
+        return self._flash(v, m, num_obj)[9]
+
+    def seed_counts(self, v, k, shared=None, filtered=True):
+        """all_counts [2,P] of mask k of view v (run_3d_seg.py:86-104).  `shared` = view_counts(v): the masks of a
+        view do not overlap, so the binary render's row 1 is the multi-label row k and its row 0 the sum of all
+        other rows; without it the reference's binary render (gt_mask in {0,1}, obj_num=1) is issued."""
+        if shared is not None:
+            counts = torch.stack([shared.sum(dim=0) - shared[k], shared[k]], dim=0)
+        else:
+            binary = (self.id_masks[v] == float(k)).to(torch.float32)
+            counts = self._flash(v, binary, 1)[9].clone()
+        if filtered:
+            counts[1:, self.pts_filter] = 0
+        return counts
+
+    @staticmethod
+    def labels_of(counts):
+        """Row 1 of counts_to_obj_labels: the Gaussians of the object (bool [P])."""
+        return multi_instance_opt(counts, 0.0)[1]
+
+    # -- matching
+    def _view_ids(self, v):
+        if v not in self._ids:
+            ids = self.id_masks[v].to(torch.int64)
+            self._ids[v] = (ids, torch.bincount(ids.reshape(-1)))
+        return self._ids[v]
+
+    def render_subset_alpha(self, v, used_mask):
+        """flashsplat_render(used_mask=...)['alpha'] (gaussian_renderer/__init__.py:154-186): the selected Gaussians
+        alone.  gt_mask is None there (all-ones labels, obj_num 2) and only alpha is read, so the plain forward of
+        the same blend is issued (alpha is the same arithmetic in both flavours)."""
+        g, c = self.g, self.cams[v]
+        self.renders += 1
+        out = _ops.rasterize_gaussians(self.bg, g["means3D"][used_mask], _E, g["opacities"][used_mask],
+                                       g["scales"][used_mask], g["rotations"][used_mask], 1.0, _E, c["viewmatrix"],
+                                       c["projmatrix"], c["tanfovx"], c["tanfovy"], c["image_height"], c["image_width"],
+                                       g["shs"][used_mask], self.deg, c["campos"], False, False)
+        return out[3]
+
+    def find_match(self, views, used_mask):
+        """[(view, mask index, iou)] for the views whose best mask has IoU > threshold (run_3d_seg.py:116-173)."""
+        if not views:
+            return []
+        best = torch.zeros((len(views), 2), dtype=torch.float64, device=self.dev)
+        for i, v in enumerate(views):
+            pred = self.render_subset_alpha(v, used_mask)[0] > 0.5
+            ids, area = self._view_ids(v)
+            best[i] = best_mask_iou(pred, ids, area)
+        res = best.cpu().tolist()                          # one read-back for all views
+        return [(v, int(k), iou) for v, (iou, k) in zip(views, res) if iou > self.iou_threshold and iou > 0.0]
+
+    # -- the loop
+    def segment_seed(self, v, k, shared=None, max_rounds=99):
+        """run_3d_seg.py:263-315 for the seed mask k of view v.  Returns None when no Gaussian is identified (:265),
+        else {"used_mask", "all_counts", "matched": [(view, mask)], "rounds"}."""
+        all_views = list(range(len(self.cams)))
+        counts = self.seed_counts(v, k, shared=shared)
+        used = self.labels_of(counts)
+        if int(used.sum().item()) == 0:
+            return None
+        matched = [(v, k)]
+        new = self.find_match([u for u in all_views if u != v], used)
+        matched += [(u, j) for u, j, _ in new]
+        rounds = 0
+        while new and rounds < max_rounds:
+            rounds += 1
+            for u, j, _ in new:                            # opt_label_w_seg(new views, new masks), no pts_filter (:301)
+                counts += self.seed_counts(u, j, filtered=False)
+            used = self.labels_of(counts)
+            done = {u for u, _ in matched}
+            new = self.find_match([u for u in all_views if u not in done], used)
+            matched += [(u, j) for u, j, _ in new]
+        return {"used_mask": used, "all_counts": counts, "matched": matched, "rounds": rounds}
