@@ -746,7 +746,7 @@ def run_orbit(args, job, workload, steps, warmup, with_e2e=True):
 # ----------------------------------------------------------------------------- label votes (cfg3)
 def make_masks(sc, cams, nobj, views):
     from wheat_3dgs_b200 import scene
-    return {v: scene.head_masks(sc, cams[v], n_labels=nobj) for v in views}
+    return {v: scene.head_masks(sc, cams[v], n_labels=nobj, solid=True) for v in views}
 
 
 def run_votes(args, job, workload, steps, warmup):

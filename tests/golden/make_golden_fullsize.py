@@ -79,12 +79,13 @@ def votes_golden(name):
 
     a1, a2 = run(), run()
     spread = float((a1 - a2).abs().max())
+    spread_g = (a1 - a2).abs().sum(dim=0)        # per Gaussian: how far its votes move between two reference runs
     s = a1.sum(dim=0)
     lab = torch.zeros_like(a1).bool()
     for k in range(a1.shape[0]):   # run_3d_seg.py:54-72
         oc = torch.stack([s - a1[k], a1[k]], dim=0)
         lab[k] = torch.argmax(torch.nn.functional.normalize(oc, dim=0), dim=0)
-    near = int(((2 * a1 - s[None]).abs() <= 4 * spread).logical_and(s[None] > 0).sum())
+    near = int(((2 * a1 - s[None]).abs() <= 4 * spread_g[None] + 1e-6 * s[None]).logical_and(s[None] > 0).sum())
     return {"views": views, "label_row_sums": lab.sum(dim=1).cpu().tolist(), "near_ties": near,
             "votes_run_to_run_spread": spread, "labelled": int(lab[1:].any(dim=0).sum())}
 

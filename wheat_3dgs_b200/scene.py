@@ -156,10 +156,12 @@ def loss_gradients(color_shape, seed=2):
     }
 
 
-def head_masks(scene, cam, n_labels=None, dilate=6):
+def head_masks(scene, cam, n_labels=None, dilate=6, solid=False):
     """Synthetic per-view instance-id mask f32[H,W] (0 = background, k = head k) made by
     splatting each head's projected Gaussian centres and dilating -- stands in for the
-    YOLO/SAM masks of run_3d_seg.py / the seg2d ids of render_360.py:62-69."""
+    YOLO/SAM masks of run_3d_seg.py / the seg2d ids of render_360.py:62-69.  The dilation
+    stamps every second pixel; `solid` closes the lattice with a 3x3 fill, which is what a SAM
+    mask looks like to find_match's IoU (run_3d_seg.py:134-157)."""
     H, W = cam["image_height"], cam["image_width"]
     hid = scene["head_id"]
     m = scene["means3D"].astype(np.float64)
@@ -177,4 +179,16 @@ def head_masks(scene, cam, n_labels=None, dilate=6):
             x = np.clip(xi + dx, 0, W - 1)
             y = np.clip(yi + dy, 0, H - 1)
             mask[y, x] = lab
+    if solid:
+        filled = mask.copy()
+        for dy in (-1, 0, 1):
+            for dx in (-1, 0, 1):
+                if dx == 0 and dy == 0:
+                    continue
+                sh = np.zeros_like(mask)
+                ys, yd = (slice(max(dy, 0), H + min(dy, 0)), slice(max(-dy, 0), H + min(-dy, 0)))
+                xs, xd = (slice(max(dx, 0), W + min(dx, 0)), slice(max(-dx, 0), W + min(-dx, 0)))
+                sh[yd, xd] = mask[ys, xs]
+                filled = np.where(filled == 0, sh, filled)
+        mask = filled
     return mask
