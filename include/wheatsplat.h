@@ -278,6 +278,9 @@ int ws_reset_opacity(int32_t P, float *opacity, float *exp_avg, float *exp_avg_s
  * buffer before it, and follow it with a barrier before reading the sums.  num_ctas <= 0: one CTA per SM. */
 int ws_allreduce_sum_f32(int32_t rank, int32_t world, int64_t numel, void *multicast_ptr, void *const *peer_ptrs,
                          int32_t num_ctas, ws_stream_t stream);
+/* Tuning knobs of the multimem kernel (process-wide): independent 16-byte ld_reduce in flight per thread (2, 4 or 8;
+ * default 4) and threads per CTA (default 512). */
+int ws_allreduce_tune(int32_t unroll, int32_t threads);
 
 /* Exchange + optimiser step of data-parallel training fused into ONE kernel (reduce-scatter, Adam, all-gather):
  * rank r owns the r-th slice of the flat parameter space [0, numel).  It reads the slice's gradient SUM over ranks

@@ -28,20 +28,23 @@ __device__ __forceinline__ void mc_st(float4 *mc, float4 v)
                  :: "l"(mc), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
 }
 
-constexpr int AR_UNROLL = 4;
+// UNROLL independent 16-byte ld_reduce per thread are in flight before the first store: the switch round trip
+// (several microseconds) times the link rate is the data that has to be outstanding (ws_allreduce_tune).
+template <int UNROLL>
 __global__ void __launch_bounds__(512) allreduce_multimem(float4 *mc, size_t begin4, size_t end4)
 {
     const size_t stride = (size_t)gridDim.x * blockDim.x;
     size_t i = begin4 + (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    for (; i + (AR_UNROLL - 1) * stride < end4; i += AR_UNROLL * stride) {
-        float4 v[AR_UNROLL];
+    for (; i + (UNROLL - 1) * stride < end4; i += UNROLL * stride) {
+        float4 v[UNROLL];
 #pragma unroll
-        for (int k = 0; k < AR_UNROLL; k++) v[k] = mc_ld_reduce(mc + i + k * stride);
+        for (int k = 0; k < UNROLL; k++) v[k] = mc_ld_reduce(mc + i + k * stride);
 #pragma unroll
-        for (int k = 0; k < AR_UNROLL; k++) mc_st(mc + i + k * stride, v[k]);
+        for (int k = 0; k < UNROLL; k++) mc_st(mc + i + k * stride, v[k]);
     }
     for (; i < end4; i += stride) mc_st(mc + i, mc_ld_reduce(mc + i));
 }
+static int g_ar_unroll = 4, g_ar_threads = 512;
 
 constexpr int AR_MAX_WORLD = 16;
 struct PeerPtrs { float4 *p[AR_MAX_WORLD]; };
@@ -135,6 +138,16 @@ __global__ void __launch_bounds__(512) sharded_adam(const ShardAdamParams P)
 
 using namespace ws;
 
+extern "C" int ws_allreduce_tune(int32_t unroll, int32_t threads)
+{
+    if ((unroll != 2 && unroll != 4 && unroll != 8) || threads < 32 || threads > 512 || threads % 32) {
+        set_error("ws_allreduce_tune: unroll 2|4|8, threads a multiple of 32 up to 512");
+        return WS_E_INVALID;
+    }
+    ws::g_ar_unroll = unroll; ws::g_ar_threads = threads;
+    return WS_OK;
+}
+
 extern "C" int ws_allreduce_sum_f32(int32_t rank, int32_t world, int64_t numel, void *multicast_ptr,
                                     void *const *peer_ptrs, int32_t num_ctas, ws_stream_t stream)
 {
@@ -152,7 +165,10 @@ extern "C" int ws_allreduce_sum_f32(int32_t rank, int32_t world, int64_t numel, 
     const int ctas = num_ctas > 0 ? num_ctas : 148;
     if (multicast_ptr) {
         if (((uintptr_t)multicast_ptr & 15) != 0) { set_error("ws_allreduce_sum_f32: multicast pointer not 16-byte aligned"); return WS_E_INVALID; }
-        allreduce_multimem<<<ctas, 512, 0, st>>>((float4 *)multicast_ptr, begin4, end4);
+        const int th = ws::g_ar_threads;
+        if (ws::g_ar_unroll >= 8) allreduce_multimem<8><<<ctas, th, 0, st>>>((float4 *)multicast_ptr, begin4, end4);
+        else if (ws::g_ar_unroll <= 2) allreduce_multimem<2><<<ctas, th, 0, st>>>((float4 *)multicast_ptr, begin4, end4);
+        else allreduce_multimem<4><<<ctas, th, 0, st>>>((float4 *)multicast_ptr, begin4, end4);
     } else {
         PeerPtrs pp;
         for (int k = 0; k < world; k++) {
