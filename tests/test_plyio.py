@@ -1,6 +1,9 @@
 """CPU: the Gaussian PLY format of GaussianModel.save_ply / load_ply (scene/gaussian_model.py:196-293).  Parity with
 plyfile-written bytes is unpinned (plyfile is not installed here); these tests cover what the reference's code fixes:
 attribute order, the [P,C,3] -> f_*_{c*?} transposes, round trips, optional / reordered properties."""
+import json
+import os
+
 import numpy as np
 import pytest
 
@@ -59,3 +62,20 @@ def test_load_tolerates_reordered_missing_and_ascii(tmp_path):
     assert np.array_equal(back["which_object"], np.zeros((5, 1), np.int32))
     with pytest.raises(ValueError):
         plyio.load_ply(path, max_sh_degree=3)                                 # the reference asserts the f_rest count
+
+
+def test_hand_built_fixture_loads_and_resaves_byte_for_byte(tmp_path):
+    """tests/golden/point_cloud_fixture.ply is packed with `struct` by tests/golden/make_golden_ply.py in the column
+    order of save_ply (scene/gaussian_model.py:212-237): load_ply must return GaussianModel's layouts (:239-293, the
+    f_rest reshape to [P,3,15] and transpose to [P,15,3]) and save_ply must reproduce the file byte for byte."""
+    gold = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+    path = os.path.join(gold, "point_cloud_fixture.ply")
+    want = json.load(open(os.path.join(gold, "point_cloud_fixture.json")))
+    got = plyio.load_ply(path, max_sh_degree=want["sh_degree"])
+    for k, v in want["params"].items():
+        ref = np.asarray(v, dtype=np.int32 if k == "which_object" else np.float32)
+        assert got[k].shape == ref.shape and got[k].dtype == ref.dtype, k
+        assert np.array_equal(got[k], ref), k
+    out = str(tmp_path / "resaved.ply")
+    plyio.save_ply(out, **got)
+    assert open(out, "rb").read() == open(path, "rb").read()
