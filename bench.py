@@ -243,19 +243,22 @@ class ResultReader:
             self.pending = None
 
 
-def stage_model(P, V, R, T, HW, M, npass, n_eval, n_contrib):
+def stage_model(P, V, R, T, HW, M, npass, n_eval, n_contrib, Rf=None):
     """Algorithmic HBM bytes / flops per view of every stage (DESIGN.md section 3 derives them)."""
     c = 12 * M  # SH bytes per Gaussian
+    Rf = R if Rf is None else Rf
     by = {
         # depth-first binning (default): preprocess also writes the (depth bits, id) pair; "sort" =
         # the depth sort of P 8-byte pairs + the tile sort of R 8-byte pairs (npass passes)
-        "preprocess": P * (44 + 8 + 8) + V * (c + 49),
+        "preprocess": P * (44 + 8 + 8) + V * (c + 65),
         "scan": 8 * ((P + 255) // 256),
-        "emit_keys": 12 * P + 8 * ((P + 255) // 256) + 24 * V + 8 * R,
+        "emit_keys": 12 * P + 8 * ((P + 255) // 256) + 40 * V + 8 * R,
         "sort": (4 * P + 4 * 16 * P) + (4 * R + npass * 16 * R),
-        "ranges_pack": 8 * R + 48 * R + 8 * T,
-        "render_fwd": 48 * R + 24 * HW,
-        "render_bwd": 48 * R + 32 * HW + 40 * V,
+        # identify_ranges reads the sorted tile keys only; the blend kernels read the value list and gather the
+        # 64-byte rows of the instances whose quadrant mask is not empty (Rf of them) from the per-Gaussian table
+        "ranges_pack": 4 * R + 8 * T,
+        "render_fwd": 4 * R + 64 * Rf + 24 * HW,
+        "render_bwd": 4 * R + 64 * Rf + 32 * HW + 40 * V,
         "preprocess_bwd": P * (4 + 48) + V * (44 + c) + P * (c + 92),
     }
     fl = {"render_fwd": 11 * n_eval + 17 * n_contrib, "render_bwd": 13 * n_eval + 60 * n_contrib}
@@ -559,7 +562,7 @@ def run_fwdbwd(args, job):
     del params, means2D, pre, gts
 
     # ---- leg 3: per-stage CUDA events (library-recorded, launching stream) + work counters
-    stats = {"V": 0, "R": 0, "n_eval": 0, "n_contrib": 0}
+    stats = {"V": 0, "R": 0, "n_eval": 0, "n_contrib": 0, "quad_pairs": 0, "instances_never_fetched": 0}
     ops.prof_enable(True)
     torch.cuda.synchronize()
     ops.prof_read()
@@ -568,9 +571,11 @@ def run_fwdbwd(args, job):
         fw = step(args.warmup + i, reduce=False)
         stats["R"] += fw[0]
         stats["V"] += int((fw[4] > 0).sum())
-        ne, nc = ops.count_pairs(W, H, fw[0], fw[6], fw[7])
+        ne, nc, nq, nz = ops.count_pairs(P, W, H, fw[0], fw[5], fw[6], fw[7])
         stats["n_eval"] += ne
         stats["n_contrib"] += nc
+        stats["quad_pairs"] += nq
+        stats["instances_never_fetched"] += nz
     torch.cuda.synchronize()
     prof = ops.prof_read()
     ops.prof_enable(False)
@@ -1244,7 +1249,8 @@ def main():
         st = r["stats"]
         T = ((W + 15) // 16) * ((H + 15) // 16)
         bits = max(1, int(np.ceil(np.log2(T + 1))))  # tile-id bits sorted per instance (depth-first binning)
-        by, fl = stage_model(P, st["V"], st["R"], T, W * H, r["M"], (bits + 7) // 8, st["n_eval"], st["n_contrib"])
+        by, fl = stage_model(P, st["V"], st["R"], T, W * H, r["M"], (bits + 7) // 8, st["n_eval"], st["n_contrib"],
+                             Rf=st["R"] - st["instances_never_fetched"])
         stages = {}
         for name, (ms, calls) in r["prof"].items():
             per = ms / max(r["nprof"], 1)
@@ -1285,7 +1291,11 @@ def main():
         value = world * args.steps / (r["ms_total"] * 1e-3)
         line = dict(base, impl="ours", value=value, ms_per_step=r["ms_total"] / args.steps, clocks=r["clocks"],
                     gpu_launches=r["launches"], roofline=roof, stages=stages, parallelism=par,
-                    work_per_view={k: st[k] for k in ("V", "R", "n_eval", "n_contrib")}, parity=r["parity"],
+                    work_per_view=dict({k: st[k] for k in ("V", "R", "n_eval", "n_contrib", "quad_pairs",
+                                                           "instances_never_fetched")},
+                                       quad_cull_survival=st["quad_pairs"] / max(4.0 * st["R"], 1.0),
+                                       pixel_slots_per_contributing_pair=64.0 * st["quad_pairs"] / max(st["n_contrib"], 1.0)),
+                    parity=r["parity"],
                     e2e={"value": world * args.steps / (r["ms_e2e"] * 1e-3), "unit": "views/s",
                          "h2d_bytes_per_step": r["h2d"], "d2h_bytes_per_step": r["d2h"]})
         if extra:

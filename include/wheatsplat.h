@@ -48,7 +48,7 @@ typedef struct CUstream_st *ws_stream_t;
 #define WS_E_CUDA (-3)      /* a CUDA runtime call or kernel launch failed */
 #define WS_E_UNSUPPORTED (-4)
 
-#define WS_ABI_VERSION 2
+#define WS_ABI_VERSION 3
 
 /* Per-view constants = GaussianRasterizationSettings
  * (DGR/diff_gaussian_rasterization/__init__.py:160-172; FSR adds mask_grad, num_obj:
@@ -198,7 +198,7 @@ int64_t ws_objeval_prepare(const ws_view *view, const ws_gaussians *g, const ws_
 int64_t ws_objeval_bin(const ws_view *view, const ws_gaussians *g, const ws_objsets *sets, const int32_t *radii,
                        void *geom, void *binning, size_t binning_bytes, void *scratch, size_t scratch_bytes,
                        int64_t num_instances, ws_stream_t stream);
-int ws_objeval_render(const ws_view *view, const ws_objsets *sets, void *binning, void *scratch,
+int ws_objeval_render(const ws_view *view, const ws_objsets *sets, int32_t P, void *geom, void *binning, void *scratch,
                       size_t scratch_bytes, int64_t num_instances, int64_t num_jobs, float *job_out,
                       size_t job_out_bytes, float *pred_mask, ws_stream_t stream);
 
@@ -349,9 +349,11 @@ const char *ws_prof_stage_name(int32_t stage);
 /* Work counters of a finished forward, for the blend kernels' flop figures:
  * counts[0] = N_eval = sum over pixels of n_contrib (pairs traversed up to the last contributor),
  * counts[1] = N_contrib = pairs among those with power <= 0 and alpha >= 1/255.
- * counts is device uint64[2], zeroed by the call. */
-int ws_debug_count_pairs(int32_t width, int32_t height, void *binning, void *image, int64_t num_rendered,
-                         uint64_t *counts, ws_stream_t stream);
+ * counts[2] = (warp, instance) pairs the 8x8 quadrant masks let through (4 x instances without the cull),
+ * counts[3] = instances whose mask is empty (never fetched by the blend kernels).
+ * counts is device uint64[4], zeroed by the call. */
+int ws_debug_count_pairs(int32_t P, int32_t width, int32_t height, void *geom, void *binning, void *image,
+                         int64_t num_rendered, uint64_t *counts, ws_stream_t stream);
 
 /* FP32 issue-rate probe (bench.py's measured roofline denominator for the blend kernels): `ctas` CTAs of 256
  * threads each run iters x 32 dependent-chain FMAs (8 independent chains, three register operands); packed != 0

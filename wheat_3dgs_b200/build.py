@@ -29,14 +29,16 @@ def build_variant(name, defines):
     vdir = os.path.join(HERE, "variants")
     os.makedirs(os.path.join(vdir, name), exist_ok=True)
     out = os.path.join(vdir, "lib%s.so" % name)
-    objs = []
-    for src in SOURCES:
+    def cc(src):
         obj = os.path.join(vdir, name, src.replace(".cu", ".o"))
         cmd = [NVCC] + FLAGS + ["-D" + d for d in defines] + ["-c", os.path.join(CSRC, src), "-o", obj]
         r = subprocess.run(cmd, capture_output=True, text=True)
         if r.returncode != 0:
             raise RuntimeError(r.stderr[-4000:])
-        objs.append(obj)
+        return obj
+
+    with ThreadPoolExecutor(max_workers=8) as ex:
+        objs = list(ex.map(cc, SOURCES))
     r = subprocess.run([NVCC, "-shared", "-o", out] + objs + ["-ccbin", "/usr/bin/g++"], capture_output=True, text=True)
     if r.returncode != 0:
         raise RuntimeError(r.stderr[-4000:])

@@ -99,6 +99,13 @@ uint32_t get_higher_msb(uint32_t n)
     return msb;
 }
 
+// the sorted pairs end in the "a" buffers after an even number of radix passes, else in "b"
+const uint32_t *sorted_vals(const BinningState &bs, int T)
+{
+    const int end_bit = (binning_keys64() ? 32 : 0) + (int)get_higher_msb((uint32_t)T);
+    return (((end_bit + 7) / 8) & 1) ? bs.vals_b : bs.vals_a;
+}
+
 int check_view_gauss(const char *who, const ws_view *v, const ws_gaussians *g, bool need_opacity)
 {
     if (!v || !g) { set_error("%s: NULL view/gaussians", who); return WS_E_INVALID; }
@@ -276,9 +283,9 @@ extern "C" int ws_forward_render(const ws_view *view, const ws_gaussians *g, con
         { ProfScope ps(3, st); rc = launch_sort_pairs32(R, bs.tkeys_a, bs.tkeys_b, bs.vals_a, bs.vals_b, end_bit, bs.sort, st, debug, &tkeys, &vals); }
         if (rc != WS_OK) return rc;
     }
-    { ProfScope ps(4, st); rc = launch_ranges_pack(R, T, keys, tkeys, vals, gs, bs, is, st, debug); }
+    { ProfScope ps(4, st); rc = launch_identify_ranges(R, T, keys, tkeys, is.ranges, st, debug); }
     if (rc != WS_OK) return rc;
-    { ProfScope ps(5, st); rc = launch_render_fwd(view, g->P, gs, bs, is, out_color, out_depth, out_alpha, fl, st); }
+    { ProfScope ps(5, st); rc = launch_render_fwd(view, g->P, gs, vals, is, out_color, out_depth, out_alpha, fl, st); }
     return rc;
 }
 
@@ -307,19 +314,18 @@ extern "C" int ws_backward(const ws_view *view, const ws_gaussians *g, const int
     GeomState gs = GeomState::from((char *)geom, (size_t)g->P);
     ImageState is = ImageState::from((char *)image, (size_t)T, (size_t)W * H);
     BinningState bs = BinningState::from((char *)binning, (size_t)num_rendered);
-    { ProfScope ps(6, st); rc = launch_render_bwd(view, g->P, gs, bs, is, out_alpha, dL_dcolor, dL_ddepth, dL_dalpha, fl, st); }
+    { ProfScope ps(6, st); rc = launch_render_bwd(view, g->P, gs, sorted_vals(bs, T), is, out_alpha, dL_dcolor, dL_ddepth, dL_dalpha, fl, st); }
     if (rc != WS_OK) return rc;
     { ProfScope ps(7, st); rc = launch_preprocess_bwd(view, g, radii, gs, gr, st); }
     return rc;
 }
 
 namespace ws {
-__global__ void unpack_geom(int P, int what, const float4 *__restrict__ g0, const float4 *__restrict__ g1,
-                            const float4 *__restrict__ g2, float *__restrict__ dst)
+__global__ void unpack_geom(int P, int what, const GRec *__restrict__ grec, float *__restrict__ dst)
 {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= P) return;
-    const float4 a = g0[i], b = g1[i], c = g2[i];
+    const float4 a = grec[i].a, b = grec[i].b, c = grec[i].c;
     if (what == 0) dst[i] = b.z;                                              // depths
     else if (what == 1) { dst[2 * i] = a.x; dst[2 * i + 1] = a.y; }          // means2D
     else if (what == 2) { dst[4 * i] = a.z; dst[4 * i + 1] = a.w; dst[4 * i + 2] = b.x; dst[4 * i + 3] = b.y; }
@@ -329,25 +335,34 @@ __global__ void unpack_geom(int P, int what, const float4 *__restrict__ g0, cons
 
 namespace ws {
 __global__ void rebuild_keys64(size_t R, const uint32_t *__restrict__ tkeys, const uint32_t *__restrict__ vals,
-                               const float4 *__restrict__ g1, uint64_t *__restrict__ keys)
+                               const GRec *__restrict__ grec, uint64_t *__restrict__ keys)
 {
     const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < R) keys[i] = ((uint64_t)tkeys[i] << 32) | __float_as_uint(g1[vals[i]].z);
+    if (i < R) keys[i] = ((uint64_t)tkeys[i] << 32) | __float_as_uint(grec[vals[i] & WS_ID_MASK].b.z);
 }
-// one thread per pixel: re-walks its tile's packed records up to the pixel's last contributor
+// point_list as the reference holds it: the Gaussian ids without the quadrant masks
+__global__ void strip_masks(size_t R, const uint32_t *__restrict__ vals, uint32_t *__restrict__ dst)
+{
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < R) dst[i] = vals[i] & WS_ID_MASK;
+}
+// one thread per pixel: re-walks its tile's list up to the pixel's last contributor.  counts[0] = pairs walked,
+// [1] = contributing pairs, [2] = (warp, record) pairs the 8x8 quadrant masks let through, [3] = instances with an
+// empty mask (never fetched by the blend kernels)
 __global__ void __launch_bounds__(256) count_pairs(int W, int H, const uint2 *__restrict__ ranges,
                                                    const uint32_t *__restrict__ n_contrib,
-                                                   const float4 *__restrict__ q0, const float4 *__restrict__ q1,
+                                                   const uint32_t *__restrict__ vals, const GRec *__restrict__ grec,
                                                    unsigned long long *__restrict__ counts)
 {
     const int px = blockIdx.x * WS_BLOCK_X + (threadIdx.x & 15), py = blockIdx.y * WS_BLOCK_Y + (threadIdx.x >> 4);
-    unsigned long long ne = 0, nc = 0;
+    unsigned long long ne = 0, nc = 0, nq = 0, nz = 0;
+    const uint2 range = ranges[blockIdx.y * gridDim.x + blockIdx.x];
     if (px < W && py < H) {
-        const uint2 range = ranges[blockIdx.y * gridDim.x + blockIdx.x];
         const uint32_t last = n_contrib[(size_t)py * W + px];
         ne = last;
         for (uint32_t k = 0; k < last; k++) {
-            const float4 a = q0[range.x + k], q = q1[range.x + k];
+            const GRec *rec = grec + (vals[range.x + k] & WS_ID_MASK);
+            const float4 a = rec->a, q = rec->b;
             const float dx = a.x - (float)px, dy = a.y - (float)py;
             const float power = -0.5f * (a.z * dx * dx + q.x * dy * dy) - a.w * dx * dy;
             if (power > 0.0f) continue;
@@ -355,11 +370,20 @@ __global__ void __launch_bounds__(256) count_pairs(int W, int H, const uint2 *__
             nc++;
         }
     }
+    for (uint32_t k = threadIdx.x; k < range.y - range.x; k += 256) {
+        const uint32_t m = vals[range.x + k] >> WS_ID_BITS;
+        nq += __popc(m);
+        nz += m == 0u;
+    }
     for (int o = 16; o > 0; o >>= 1) {
         ne += __shfl_xor_sync(0xffffffffu, ne, o);
         nc += __shfl_xor_sync(0xffffffffu, nc, o);
+        nq += __shfl_xor_sync(0xffffffffu, nq, o);
+        nz += __shfl_xor_sync(0xffffffffu, nz, o);
     }
-    if ((threadIdx.x & 31) == 0) { atomicAdd(counts, ne); atomicAdd(counts + 1, nc); }
+    if ((threadIdx.x & 31) == 0) {
+        atomicAdd(counts, ne); atomicAdd(counts + 1, nc); atomicAdd(counts + 2, nq); atomicAdd(counts + 3, nz);
+    }
 }
 } // namespace ws
 
@@ -417,10 +441,10 @@ extern "C" int64_t ws_debug_fma_peak(int32_t packed, int32_t iters, int32_t ctas
     return (int64_t)ctas * 256 * (int64_t)iters * 32 * 2 * (packed ? 2 : 1);
 }
 
-extern "C" int ws_debug_count_pairs(int32_t width, int32_t height, void *binning, void *image, int64_t num_rendered,
-                                    uint64_t *counts, ws_stream_t stream)
+extern "C" int ws_debug_count_pairs(int32_t P, int32_t width, int32_t height, void *geom, void *binning, void *image,
+                                    int64_t num_rendered, uint64_t *counts, ws_stream_t stream)
 {
-    if (!image || !counts || width <= 0 || height <= 0 || (num_rendered > 0 && !binning)) {
+    if (!geom || !image || !counts || P <= 0 || width <= 0 || height <= 0 || (num_rendered > 0 && !binning)) {
         set_error("ws_debug_count_pairs: bad arguments");
         return WS_E_INVALID;
     }
@@ -428,9 +452,10 @@ extern "C" int ws_debug_count_pairs(int32_t width, int32_t height, void *binning
     const int gx = (width + WS_BLOCK_X - 1) / WS_BLOCK_X, gy = (height + WS_BLOCK_Y - 1) / WS_BLOCK_Y;
     ImageState is = ImageState::from((char *)image, (size_t)gx * gy, (size_t)width * height);
     BinningState bs = BinningState::from((char *)binning, (size_t)num_rendered);
-    WS_CUDA_CHECK(cudaMemsetAsync(counts, 0, 16, st));
-    ws::count_pairs<<<dim3(gx, gy), 256, 0, st>>>(width, height, is.ranges, is.n_contrib, bs.q0, bs.q1,
-                                                 (unsigned long long *)counts);
+    GeomState gs = GeomState::from((char *)geom, (size_t)P);
+    WS_CUDA_CHECK(cudaMemsetAsync(counts, 0, 32, st));
+    ws::count_pairs<<<dim3(gx, gy), 256, 0, st>>>(width, height, is.ranges, is.n_contrib, ws::sorted_vals(bs, gx * gy),
+                                                 gs.grec, (unsigned long long *)counts);
     WS_LAUNCH_CHECK(st, false);
     return WS_OK;
 }
@@ -454,7 +479,7 @@ extern "C" int64_t ws_debug_fetch(const char *name, int32_t P, int32_t width, in
         // only rows of visible Gaussians are meaningful (the reference leaves the rest stale too)
         if (dst_bytes < need) { set_error("ws_debug_fetch: dst too small"); return WS_E_SCRATCH; }
         WS_CUDA_CHECK(cudaMemsetAsync(dst, 0, need, st));
-        ws::unpack_geom<<<(P + 255) / 256, 256, 0, st>>>(P, what, gs.g0, gs.g1, gs.g2, (float *)dst);
+        ws::unpack_geom<<<(P + 255) / 256, 256, 0, st>>>(P, what, gs.grec, (float *)dst);
         WS_LAUNCH_CHECK(st, false);
         return (int64_t)need;
     }
@@ -472,14 +497,20 @@ extern "C" int64_t ws_debug_fetch(const char *name, int32_t P, int32_t width, in
         const int end_bit = (k64 ? 32 : 0) + (int)ws::get_higher_msb((uint32_t)T);
         const int npass = (end_bit + 7) / 8;
         const bool in_b = (npass & 1) != 0;
-        if (!strcmp(name, "point_list")) { src = in_b ? bs.vals_b : bs.vals_a; need = 4 * R; }
+        if (!strcmp(name, "point_list")) {
+            need = 4 * R;
+            if (dst_bytes < need) { set_error("ws_debug_fetch: dst too small"); return WS_E_SCRATCH; }
+            ws::strip_masks<<<(unsigned)((R + 255) / 256), 256, 0, st>>>(R, in_b ? bs.vals_b : bs.vals_a, (uint32_t *)dst);
+            WS_LAUNCH_CHECK(st, false);
+            return (int64_t)need;
+        }
         else if (k64) { src = in_b ? bs.keys_b : bs.keys_a; need = 8 * R; }
         else {
             // depth-first binning sorts tile ids only: rebuild the reference's tile|depth keys
             need = 8 * R;
             if (dst_bytes < need) { set_error("ws_debug_fetch: dst too small"); return WS_E_SCRATCH; }
             ws::rebuild_keys64<<<(unsigned)((R + 255) / 256), 256, 0, st>>>(
-                R, in_b ? bs.tkeys_b : bs.tkeys_a, in_b ? bs.vals_b : bs.vals_a, gs.g1, (uint64_t *)dst);
+                R, in_b ? bs.tkeys_b : bs.tkeys_a, in_b ? bs.vals_b : bs.vals_a, gs.grec, (uint64_t *)dst);
             WS_LAUNCH_CHECK(st, false);
             return (int64_t)need;
         }

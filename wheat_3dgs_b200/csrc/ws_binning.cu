@@ -1,11 +1,12 @@
-// ws_binning.cu -- identify_ranges_pack: one pass over the sorted instance list that
-//   (a) writes the per-tile [start,end) ranges (replaces identifyTileRanges,
-//       DGR rasterizer_impl.cu:116-138, after the cudaMemset of :311), and
-//   (b) gathers each instance's per-Gaussian record into tile order (q0,q1,q2), so the blend
-//       kernels read contiguous 16-byte records with TMA bulk copies instead of gathering
-//       through point_list inside the pixel loop (DGR forward.cu:321-324,359,361).
-// Algorithmic HBM bytes: 8R read (tile key + value; 12R with 64-bit keys) + 48R written; the 48-byte gathers hit L2
-// (the per-Gaussian arrays are 48 B x P = 48 MB at 1 M Gaussians, L2 is 126 MB).
+// ws_binning.cu -- identify_ranges: one pass over the sorted tile keys that writes the per-tile [start,end)
+// ranges (replaces identifyTileRanges, DGR rasterizer_impl.cu:116-138, after the cudaMemset of :311), plus the
+// small helpers that say where the sorted list lives.
+//
+// Round 1 gathered every instance's 48-byte Gaussian record into tile order here (48 R bytes written, read again
+// by both blend kernels).  The blend kernels now gather the rows of the instances that survive the quadrant
+// cull themselves (TMA gather4 from the L2-resident per-Gaussian table), so this pass only reads the keys.
+// Algorithmic HBM bytes: 4 R read (8 R with 64-bit keys) + 8 T written.
+#include <cuda.h>
 #include "ws_common.cuh"
 
 namespace ws {
@@ -14,13 +15,7 @@ __device__ __forceinline__ uint32_t tile_of(uint64_t k) { return (uint32_t)(k >>
 __device__ __forceinline__ uint32_t tile_of(uint32_t k) { return k; }
 
 template <typename K>
-__global__ void __launch_bounds__(256) identify_ranges_pack(size_t R, const K *__restrict__ keys,
-                                                            const uint32_t *__restrict__ vals,
-                                                            const float4 *__restrict__ g0,
-                                                            const float4 *__restrict__ g1,
-                                                            const float4 *__restrict__ g2,
-                                                            uint2 *__restrict__ ranges, float4 *__restrict__ q0,
-                                                            float4 *__restrict__ q1, float4 *__restrict__ q2)
+__global__ void __launch_bounds__(256) identify_ranges(size_t R, const K *__restrict__ keys, uint2 *__restrict__ ranges)
 {
     const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= R) return;
@@ -35,27 +30,53 @@ __global__ void __launch_bounds__(256) identify_ranges_pack(size_t R, const K *_
         }
     }
     if (idx == R - 1) ranges[currtile].y = (uint32_t)R;
-    const uint32_t g = vals[idx];
-    const float4 a = __ldg(g0 + g), b = __ldg(g1 + g);
-    float4 c = __ldg(g2 + g);
-    c.w = __uint_as_float(g);
-    q0[idx] = a;
-    q1[idx] = b;
-    q2[idx] = c;
 }
 
-int launch_ranges_pack(size_t R, int T, const uint64_t *keys, const uint32_t *tkeys, const uint32_t *vals,
-                       GeomState &gs, BinningState &bs, ImageState &is, cudaStream_t st, bool debug)
+int launch_identify_ranges(size_t R, int T, const uint64_t *keys, const uint32_t *tkeys, uint2 *ranges,
+                           cudaStream_t st, bool debug)
 {
-    WS_CUDA_CHECK(cudaMemsetAsync(is.ranges, 0, (size_t)T * sizeof(uint2), st));
+    WS_CUDA_CHECK(cudaMemsetAsync(ranges, 0, (size_t)T * sizeof(uint2), st));
     if (R == 0) return WS_OK;
     if (tkeys)
-        identify_ranges_pack<uint32_t><<<(unsigned)((R + 255) / 256), 256, 0, st>>>(
-            R, tkeys, vals, gs.g0, gs.g1, gs.g2, is.ranges, bs.q0, bs.q1, bs.q2);
+        identify_ranges<uint32_t><<<(unsigned)((R + 255) / 256), 256, 0, st>>>(R, tkeys, ranges);
     else
-        identify_ranges_pack<uint64_t><<<(unsigned)((R + 255) / 256), 256, 0, st>>>(
-            R, keys, vals, gs.g0, gs.g1, gs.g2, is.ranges, bs.q0, bs.q1, bs.q2);
+        identify_ranges<uint64_t><<<(unsigned)((R + 255) / 256), 256, 0, st>>>(R, keys, ranges);
     WS_LAUNCH_CHECK(st, debug);
+    return WS_OK;
+}
+
+// TMA descriptor of the per-Gaussian table: 2-D float tensor, 16 columns x P rows, 64-byte row pitch, box 16 x 1,
+// no swizzle.  tile::gather4 then brings four rows given by four row coordinates.  The driver entry point is looked
+// up through the runtime (no link-time dependency on libcuda).
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                  const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+int make_grec_tensor_map(TensorMap *tm, const GRec *grec, int P)
+{
+    static_assert(sizeof(TensorMap) == sizeof(CUtensorMap), "TensorMap must have the size of CUtensorMap");
+    static EncodeTiledFn encode = nullptr;
+    if (!encode) {
+        void *fn = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q);
+        if (e != cudaSuccess || q != cudaDriverEntryPointSuccess || !fn) {
+            set_error("cuTensorMapEncodeTiled is not available from this driver (%s)", cudaGetErrorString(e));
+            return WS_E_CUDA;
+        }
+        encode = (EncodeTiledFn)fn;
+    }
+    const cuuint64_t dims[2] = {16, (cuuint64_t)(P > 0 ? P : 1)};
+    const cuuint64_t strides[1] = {sizeof(GRec)};
+    const cuuint32_t box[2] = {16, 1};
+    const cuuint32_t estr[2] = {1, 1};
+    CUresult r = encode((CUtensorMap *)tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, (void *)grec, dims, strides, box, estr,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        set_error("cuTensorMapEncodeTiled failed (%d) for the %d x 64-byte Gaussian table at %p", (int)r, P, (const void *)grec);
+        return WS_E_CUDA;
+    }
     return WS_OK;
 }
 

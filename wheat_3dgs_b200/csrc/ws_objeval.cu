@@ -51,7 +51,7 @@ __global__ void __launch_bounds__(WS_PRE_THREADS) objeval_block_sums(int P, cons
 __global__ void __launch_bounds__(WS_PRE_THREADS) objeval_emit(int P, int gx, int gy, uint32_t T,
                                                                const uint32_t *__restrict__ order,
                                                                const int32_t *__restrict__ radii,
-                                                               const float4 *__restrict__ g0,
+                                                               const GRec *__restrict__ grec,
                                                                const uint32_t *__restrict__ tiles_touched,
                                                                const int32_t *__restrict__ member_start,
                                                                const int32_t *__restrict__ member_obj,
@@ -62,6 +62,7 @@ __global__ void __launch_bounds__(WS_PRE_THREADS) objeval_emit(int P, int gx, in
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
     const int i = blockIdx.x * WS_PRE_THREADS + tid;
     uint32_t tt = 0, per = 1, rminx = 0, rminy = 0, width = 1, gid = 0, ms = 0;
+    float4 ga = make_float4(0.f, 0.f, 0.f, 0.f), gb = ga;
     if (i < P) {
         gid = order[i];
         const int rad = radii[gid];
@@ -70,9 +71,9 @@ __global__ void __launch_bounds__(WS_PRE_THREADS) objeval_emit(int P, int gx, in
         if (rad > 0 && mc > 0) {
             per = tiles_touched[gid];
             tt = per * mc;
-            const float4 a = g0[gid];
+            ga = grec[gid].a; gb = grec[gid].b;
             uint2 rmin, rmax;
-            get_rect(a.x, a.y, rad, gx, gy, rmin, rmax);
+            get_rect(ga.x, ga.y, rad, gx, gy, rmin, rmax);
             rminx = rmin.x; rminy = rmin.y; width = rmax.x - rmin.x;
             if (per == 0) { per = 1; tt = 0; }
         }
@@ -89,6 +90,7 @@ __global__ void __launch_bounds__(WS_PRE_THREADS) objeval_emit(int P, int gx, in
     uint32_t warp_base = block_offsets[blockIdx.x];
     for (int k = 0; k < w; k++) warp_base += s_w[k];
     const uint32_t excl = inc - tt;
+    const QuadTest qt = quad_test_of(ga, gb);
     for (uint32_t k0 = 0; k0 < warp_total; k0 += 32) {
         const uint32_t k = k0 + lane;
         int j = 0; // owner lane = number of lanes whose inclusive sum <= k
@@ -105,13 +107,15 @@ __global__ void __launch_bounds__(WS_PRE_THREADS) objeval_emit(int P, int gx, in
         const uint32_t o_id = __shfl_sync(0xffffffffu, gid, j);
         const uint32_t o_per = __shfl_sync(0xffffffffu, per, j);
         const uint32_t o_ms = __shfl_sync(0xffffffffu, ms, j);
+        const QuadTest oq = shfl_quad_test(qt, j);
         if (k < warp_total) {
             const uint32_t local = k - o_excl;
             const uint32_t memb = local / o_per, tl = local - memb * o_per;
             const uint32_t ty = tl / o_w, tx = tl - ty * o_w;
             const uint32_t obj = (uint32_t)__ldg(member_obj + o_ms + memb);
             tkeys[(size_t)warp_base + k] = obj * T + (o_miny + ty) * (uint32_t)gx + (o_minx + tx);
-            vals[(size_t)warp_base + k] = o_id;
+            const uint32_t qm = quad_mask(oq, (float)((o_minx + tx) * WS_BLOCK_X), (float)((o_miny + ty) * WS_BLOCK_Y));
+            vals[(size_t)warp_base + k] = o_id | (qm << WS_ID_BITS);
         }
     }
 }
@@ -407,7 +411,7 @@ extern "C" int64_t ws_objeval_bin(const ws_view *view, const ws_gaussians *g, co
     WS_LAUNCH_CHECK(st, debug);
     rc = launch_scan_u32(nb, gs.block_sums, gs.block_offsets, gs.total + 1, st, debug);
     if (rc != WS_OK) return rc;
-    objeval_emit<<<nb, WS_PRE_THREADS, 0, st>>>(g->P, gx, gy, T, order, radii, gs.g0, gs.tiles_touched,
+    objeval_emit<<<nb, WS_PRE_THREADS, 0, st>>>(g->P, gx, gy, T, order, radii, gs.grec, gs.tiles_touched,
                                                 sets->member_start, sets->member_obj, gs.block_offsets, bs.tkeys_a,
                                                 bs.vals_a);
     WS_LAUNCH_CHECK(st, debug);
@@ -417,7 +421,8 @@ extern "C" int64_t ws_objeval_bin(const ws_view *view, const ws_gaussians *g, co
     if (rc != WS_OK) return rc;
     ImageState is;
     is.ranges = os.ranges; is.n_contrib = nullptr;
-    rc = launch_ranges_pack(R, (int)VT, nullptr, tkeys, vals, gs, bs, is, st, debug);
+    (void)vals;
+    rc = launch_identify_ranges(R, (int)VT, nullptr, tkeys, is.ranges, st, debug);
     if (rc != WS_OK) return rc;
     const uint32_t jb = (VT + 255u) / 256u;
     job_block_counts<<<jb, 256, 0, st>>>(VT, os.ranges, os.jsums);
@@ -433,7 +438,7 @@ extern "C" int64_t ws_objeval_bin(const ws_view *view, const ws_gaussians *g, co
     return (int64_t)th[1];
 }
 
-extern "C" int ws_objeval_render(const ws_view *view, const ws_objsets *sets, void *binning, void *scratch,
+extern "C" int ws_objeval_render(const ws_view *view, const ws_objsets *sets, int32_t P, void *geom, void *binning, void *scratch,
                                  size_t scratch_bytes, int64_t num_instances, int64_t num_jobs, float *job_out,
                                  size_t job_out_bytes, float *pred_mask, ws_stream_t stream)
 {
@@ -444,7 +449,7 @@ extern "C" int ws_objeval_render(const ws_view *view, const ws_objsets *sets, vo
     uint32_t VT = 0;
     int rc = check_sets("ws_objeval_render", view, sets, &VT);
     if (rc != WS_OK) return rc;
-    if (!scratch || !pred_mask || num_instances < 0 || num_jobs < 0 || num_jobs > num_instances ||
+    if (!scratch || !pred_mask || !geom || P <= 0 || num_instances < 0 || num_jobs < 0 || num_jobs > num_instances ||
         (num_jobs > 0 && (!binning || !job_out))) {
         set_error("ws_objeval_render: NULL buffer or bad counts");
         return WS_E_INVALID;
@@ -468,8 +473,11 @@ extern "C" int ws_objeval_render(const ws_view *view, const ws_objsets *sets, vo
     WS_LAUNCH_CHECK(st, debug);
     if (num_jobs == 0) return WS_OK;
     BinningState bs = BinningState::from((char *)binning, (size_t)num_instances);
+    GeomState gs = GeomState::from((char *)geom, (size_t)P);
+    // the (object, tile) sort ran over get_higher_msb(VT) bits: the sorted values sit in "a" after an even pass count
+    const uint32_t *vals = ((((int)get_higher_msb(VT) + 7) / 8) & 1) ? bs.vals_b : bs.vals_a;
     float *job_alpha = job_out, *job_depth = job_out + (size_t)num_jobs * 256;
-    rc = launch_render_jobs(view, os.ranges, os.jobs, (int)num_jobs, (int)T, bs, job_alpha, job_depth, st);
+    rc = launch_render_jobs(view, P, gs, vals, os.ranges, os.jobs, (int)num_jobs, (int)T, job_alpha, job_depth, st);
     if (rc != WS_OK) return rc;
     job_obj_starts<<<(sets->num_rows + 256) / 256, 256, 0, st>>>(sets->num_rows, (int)num_jobs, T, os.jobs, os.obj_start);
     WS_LAUNCH_CHECK(st, debug);

@@ -36,7 +36,7 @@ struct PreParams {
     const float *means3D, *shs, *colors_precomp, *opacities, *scales, *rotations, *cov3D_precomp;
     const float *view, *proj, *campos;
     int32_t *radii;
-    float4 *g0, *g1, *g2;
+    GRec *grec;
     uint32_t *tiles_touched, *block_sums;
     uint32_t *dkeys, *dvals; // depth bits (culled: 0xffffffff) and Gaussian id, input of the depth sort
     uint8_t *clamped;
@@ -265,9 +265,12 @@ __global__ void __launch_bounds__(WS_PRE_THREADS) preprocess_fwd(const PreParams
                         b = p.colors_precomp[3 * (size_t)idx + 2];
                     }
                     const float opac = p.raw ? raw_sigmoid(p.opacities[idx]) : p.opacities[idx];
-                    p.g0[idx] = make_float4(pix, piy, conx, cony);
-                    p.g1[idx] = make_float4(conz, opac, pvz, logf(255.0f * opac));
-                    p.g2[idx] = make_float4(r, g, b, 0.0f);
+                    GRec rec;
+                    rec.a = make_float4(pix, piy, conx, cony);
+                    rec.b = make_float4(conz, opac, pvz, logf(255.0f * opac));
+                    rec.c = make_float4(r, g, b, 0.0f);
+                    rec.d = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+                    p.grec[idx] = rec;
                     p.clamped[idx] = cl;
                     if (p.gs_depth) p.gs_depth[idx] = pvz; // FSR forward.cu:258
                     my_rad = radius;
@@ -310,7 +313,7 @@ int launch_preprocess(const ws_view *v, const ws_gaussians *g, int32_t *radii, G
     p.cov3D_precomp = g->cov3D_precomp;
     p.shs_rest = g->shs ? g->shs_rest : nullptr; p.raw = g->raw_params;
     p.view = v->viewmatrix; p.proj = v->projmatrix; p.campos = v->campos;
-    p.radii = radii; p.g0 = gs.g0; p.g1 = gs.g1; p.g2 = gs.g2;
+    p.radii = radii; p.grec = gs.grec;
     p.tiles_touched = gs.tiles_touched; p.block_sums = gs.block_sums; p.clamped = gs.clamped;
     p.dkeys = gs.dkeys_a; p.dvals = gs.dvals_a;
     p.image_xys = fl ? fl->image_xys : nullptr;
@@ -396,8 +399,7 @@ int launch_scan_blocks(int P, GeomState &gs, cudaStream_t st, bool debug)
 // exactly the reference's (rasterizer_impl.cu:96-108), so a stable sort gives the same list.
 __global__ void __launch_bounds__(WS_PRE_THREADS) emit_keys(int P, int gx, int gy,
                                                             const int32_t *__restrict__ radii,
-                                                            const float4 *__restrict__ g0,
-                                                            const float4 *__restrict__ g1,
+                                                            const GRec *__restrict__ grec,
                                                             const uint32_t *__restrict__ tiles_touched,
                                                             const uint32_t *__restrict__ block_offsets,
                                                             uint64_t *__restrict__ keys,
@@ -407,15 +409,16 @@ __global__ void __launch_bounds__(WS_PRE_THREADS) emit_keys(int P, int gx, int g
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
     const int idx = blockIdx.x * WS_PRE_THREADS + tid;
     uint32_t tt = 0, rminx = 0, rminy = 0, width = 1, dbits = 0;
+    float4 ga = make_float4(0.f, 0.f, 0.f, 0.f), gb = ga;
     if (idx < P) {
         const int rad = radii[idx];
         if (rad > 0) {
             tt = tiles_touched[idx];
-            const float4 a = g0[idx];
+            ga = grec[idx].a; gb = grec[idx].b;
             uint2 rmin, rmax;
-            get_rect(a.x, a.y, rad, gx, gy, rmin, rmax);
+            get_rect(ga.x, ga.y, rad, gx, gy, rmin, rmax);
             rminx = rmin.x; rminy = rmin.y; width = rmax.x - rmin.x;
-            dbits = __float_as_uint(g1[idx].z);
+            dbits = __float_as_uint(gb.z);
         }
     }
     uint32_t inc = tt;
@@ -431,6 +434,7 @@ __global__ void __launch_bounds__(WS_PRE_THREADS) emit_keys(int P, int gx, int g
     for (int k = 0; k < w; k++) warp_base += s_w[k];
     const uint32_t excl = inc - tt;
     const uint32_t first_idx = blockIdx.x * WS_PRE_THREADS + w * 32;
+    const QuadTest qt = quad_test_of(ga, gb);
     for (uint32_t k0 = 0; k0 < warp_total; k0 += 32) {
         const uint32_t k = k0 + lane;
         int j = 0; // number of lanes whose inclusive sum <= k  == owner lane
@@ -445,13 +449,15 @@ __global__ void __launch_bounds__(WS_PRE_THREADS) emit_keys(int P, int gx, int g
         const uint32_t o_miny = __shfl_sync(0xffffffffu, rminy, j);
         const uint32_t o_w = __shfl_sync(0xffffffffu, width, j);
         const uint32_t o_d = __shfl_sync(0xffffffffu, dbits, j);
+        const QuadTest oq = shfl_quad_test(qt, j);
         if (k < warp_total) {
             const uint32_t local = k - o_excl;
             const uint32_t ty = local / o_w, tx = local - ty * o_w;
             uint64_t key = (uint64_t)((o_miny + ty) * (uint32_t)gx + (o_minx + tx));
             key = (key << 32) | o_d;
             keys[(size_t)warp_base + k] = key;
-            vals[(size_t)warp_base + k] = first_idx + j;
+            const uint32_t qm = quad_mask(oq, (float)((o_minx + tx) * WS_BLOCK_X), (float)((o_miny + ty) * WS_BLOCK_Y));
+            vals[(size_t)warp_base + k] = (first_idx + j) | (qm << WS_ID_BITS);
         }
     }
 }
@@ -461,7 +467,7 @@ int launch_emit_keys(int P, int W, int H, const int32_t *radii, GeomState &gs, u
 {
     const int gx = (W + WS_BLOCK_X - 1) / WS_BLOCK_X, gy = (H + WS_BLOCK_Y - 1) / WS_BLOCK_Y;
     const int nb = (P + WS_PRE_THREADS - 1) / WS_PRE_THREADS;
-    emit_keys<<<nb, WS_PRE_THREADS, 0, st>>>(P, gx, gy, radii, gs.g0, gs.g1, gs.tiles_touched,
+    emit_keys<<<nb, WS_PRE_THREADS, 0, st>>>(P, gx, gy, radii, gs.grec, gs.tiles_touched,
                                              gs.block_offsets, keys, vals);
     WS_LAUNCH_CHECK(st, debug);
     return WS_OK;
@@ -507,7 +513,7 @@ __global__ void __launch_bounds__(WS_PRE_THREADS) ordered_block_sums(int P, cons
 __global__ void __launch_bounds__(WS_PRE_THREADS) emit_tiles_ordered(int P, int gx, int gy,
                                                                      const uint32_t *__restrict__ order,
                                                                      const int32_t *__restrict__ radii,
-                                                                     const float4 *__restrict__ g0,
+                                                                     const GRec *__restrict__ grec,
                                                                      const uint32_t *__restrict__ tiles_touched,
                                                                      const uint32_t *__restrict__ block_offsets,
                                                                      uint32_t *__restrict__ tkeys,
@@ -517,14 +523,15 @@ __global__ void __launch_bounds__(WS_PRE_THREADS) emit_tiles_ordered(int P, int 
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
     const int i = blockIdx.x * WS_PRE_THREADS + tid;
     uint32_t tt = 0, rminx = 0, rminy = 0, width = 1, gid = 0;
+    float4 ga = make_float4(0.f, 0.f, 0.f, 0.f), gb = ga;
     if (i < P) {
         gid = order[i];
         const int rad = radii[gid];
         if (rad > 0) {
             tt = tiles_touched[gid];
-            const float4 a = g0[gid];
+            ga = grec[gid].a; gb = grec[gid].b;
             uint2 rmin, rmax;
-            get_rect(a.x, a.y, rad, gx, gy, rmin, rmax);
+            get_rect(ga.x, ga.y, rad, gx, gy, rmin, rmax);
             rminx = rmin.x; rminy = rmin.y; width = rmax.x - rmin.x;
         }
     }
@@ -540,6 +547,7 @@ __global__ void __launch_bounds__(WS_PRE_THREADS) emit_tiles_ordered(int P, int 
     uint32_t warp_base = block_offsets[blockIdx.x];
     for (int k = 0; k < w; k++) warp_base += s_w[k];
     const uint32_t excl = inc - tt;
+    const QuadTest qt = quad_test_of(ga, gb);
     for (uint32_t k0 = 0; k0 < warp_total; k0 += 32) {
         const uint32_t k = k0 + lane;
         int j = 0; // number of lanes whose inclusive sum <= k  == owner lane
@@ -554,11 +562,15 @@ __global__ void __launch_bounds__(WS_PRE_THREADS) emit_tiles_ordered(int P, int 
         const uint32_t o_miny = __shfl_sync(0xffffffffu, rminy, j);
         const uint32_t o_w = __shfl_sync(0xffffffffu, width, j);
         const uint32_t o_id = __shfl_sync(0xffffffffu, gid, j);
+        const QuadTest oq = shfl_quad_test(qt, j);
         if (k < warp_total) {
             const uint32_t local = k - o_excl;
             const uint32_t ty = local / o_w, tx = local - ty * o_w;
             tkeys[(size_t)warp_base + k] = (o_miny + ty) * (uint32_t)gx + (o_minx + tx);
-            vals[(size_t)warp_base + k] = o_id;
+            // which 8x8 quadrants of this tile the Gaussian can reach: the blend kernels' sub-tile cull, paid
+            // once per instance here instead of once per (warp, record) in every blend pass
+            const uint32_t qm = quad_mask(oq, (float)((o_minx + tx) * WS_BLOCK_X), (float)((o_miny + ty) * WS_BLOCK_Y));
+            vals[(size_t)warp_base + k] = o_id | (qm << WS_ID_BITS);
         }
     }
 }
@@ -573,7 +585,7 @@ int launch_emit_tiles_ordered(int P, int W, int H, const int32_t *radii, GeomSta
     WS_LAUNCH_CHECK(st, debug);
     scan_block_sums<<<1, 1024, 0, st>>>(nb, gs.block_sums, gs.block_offsets, gs.total + 1);
     WS_LAUNCH_CHECK(st, debug);
-    emit_tiles_ordered<<<nb, WS_PRE_THREADS, 0, st>>>(P, gx, gy, order, radii, gs.g0, gs.tiles_touched,
+    emit_tiles_ordered<<<nb, WS_PRE_THREADS, 0, st>>>(P, gx, gy, order, radii, gs.grec, gs.tiles_touched,
                                                       gs.block_offsets, tkeys, vals);
     WS_LAUNCH_CHECK(st, debug);
     return WS_OK;

@@ -37,7 +37,7 @@ struct PreBwdParams {
     const int32_t *radii;
     const uint8_t *clamped;
     const float *acc;
-    const float4 *g0, *g1;
+    const GRec *grec;
     float *dL_dmeans2D, *dL_dcolors, *dL_dopacity, *dL_dmeans3D, *dL_dcov3D, *dL_dsh, *dL_dscales,
         *dL_drotations;
     int sh_vec4;
@@ -171,7 +171,7 @@ __global__ void WS_PB_BOUNDS preprocess_bwd(const PreBwdParams p)
             const float4 a0 = ap[0], a1 = ap[1], a2 = ap[2];
             a[0] = a0.x; a[1] = a0.y; a[2] = a0.z; a[3] = a0.w;
             {
-                const float4 ga = p.g0[idx], gb = p.g1[idx]; // {x, y, A, B}, {C, opacity, depth, tau}
+                const float4 ga = p.grec[idx].a, gb = p.grec[idx].b; // {x, y, A, B}, {C, opacity, depth, tau}
                 const float k = -0.5f * gb.y;
                 a[4] = k * (float)p.W * (ga.z * a1.x + ga.w * a1.y);
                 a[5] = k * (float)p.H * (gb.x * a1.y + ga.w * a1.x);
@@ -358,7 +358,7 @@ __global__ void WS_PB_BOUNDS preprocess_bwd(const PreBwdParams p)
 #pragma unroll
                     for (int k = 0; k < 4; k++) drot[k] = (drot[k] - q[k] * qg) / qn;
                 }
-                const float o = p.g1[idx].y;
+                const float o = p.grec[idx].b.y;
                 a[9] *= o * (1.0f - o);
             }
         } else {
@@ -429,7 +429,7 @@ int launch_preprocess_bwd(const ws_view *v, const ws_gaussians *g, const int32_t
     p.means3D = g->means3D; p.shs = g->shs; p.scales = g->scales; p.rotations = g->rotations;
     p.cov3D_precomp = g->cov3D_precomp;
     p.view = v->viewmatrix; p.proj = v->projmatrix; p.campos = v->campos;
-    p.radii = radii; p.clamped = gs.clamped; p.acc = gs.acc; p.g0 = gs.g0; p.g1 = gs.g1;
+    p.radii = radii; p.clamped = gs.clamped; p.acc = gs.acc; p.grec = gs.grec;
     p.dL_dmeans2D = gr->dL_dmeans2D; p.dL_dcolors = gr->dL_dcolors; p.dL_dopacity = gr->dL_dopacity;
     p.dL_dmeans3D = gr->dL_dmeans3D; p.dL_dcov3D = gr->dL_dcov3D; p.dL_dsh = gr->dL_dsh;
     p.dL_dscales = gr->dL_dscales; p.dL_drotations = gr->dL_drotations;

@@ -2,10 +2,12 @@
 // DGR backward.cu:415-601; flashsplat gate FSR backward.cu:455-462,529-536).
 //
 // Same warp / lane mapping (warp = 8x8 pixels, two pixels per lane, packed
-// f32x2 arithmetic), record staging (TMA bulk copies, mbarrier double buffer) and sub-tile culling
+// f32x2 arithmetic), record staging (quadrant-mask compaction of the tile's value list, TMA gather4 copies of
+// the surviving Gaussians' rows, mbarrier double buffer) and sub-tile culling
 // as the forward (ws_render_fwd.cu), walking the tile's records back to front from the largest
 // last-contributor position in the tile (records behind it are never fetched; the reference
-// walks them with `contributor >= last_contributor -> continue`).  alpha is recomputed with the
+// walks them with `contributor >= last_contributor -> continue`).  A CTA is one half tile (two quadrants): an
+// instance is fetched only if its mask touches one of them.  alpha is recomputed with the
 // forward's exact operations, so the set of contributing pairs is the forward's.
 //
 // Per-pixel recurrence.  The reference keeps, per pixel, the colour / depth / alpha accumulated
@@ -32,23 +34,27 @@
 // H (C S g dy + B S g dx))  (backward.cu:583-598 with the constants factored out of the sums), so
 // the kernel accumulates {dL_dcolor rgb, dL_ddepth, S g dx, S g dy, S g dx^2, S g dx dy, S g dy^2, S g}
 // and preprocess_bwd applies the constants once per Gaussian.
-#include "ws_common.cuh"
+#include "ws_stage.cuh"
 
 namespace ws {
 
-#ifndef WS_RB_BATCH
-#define WS_RB_BATCH 128
-#endif
 #ifndef WS_RB_WARPS
 #define WS_RB_WARPS 2
 #endif
-constexpr int RB_BATCH = WS_RB_BATCH; // records per stage
-constexpr int RB_WARPS = WS_RB_WARPS;    // 8x8 pixel blocks (warps) per CTA: 1, 2 (a 16x8 half tile) or 4 (the tile)
+#ifndef WS_RB_NSTAGE
+#define WS_RB_NSTAGE 3
+#endif
+#ifndef WS_RB_MINB
+#define WS_RB_MINB 1
+#endif
+constexpr int RB_WARPS = WS_RB_WARPS;   // 8x8 pixel blocks (warps) per CTA: 2 = a 16x8 half tile, 4 = the tile
 constexpr int RB_THREADS = 32 * RB_WARPS;
+constexpr int RB_NSTAGE = WS_RB_NSTAGE;
+using BwdRing = StageRing<RB_WARPS, RB_NSTAGE>;
 
 struct RenderBwdParams {
     const uint2 *ranges;
-    const float4 *q0, *q1, *q2;
+    const uint32_t *vals; // sorted values: Gaussian id | quadrant mask << 28
     int W, H, tiles_x;
     const float *bg;
     const float *out_alpha;
@@ -60,19 +66,17 @@ struct RenderBwdParams {
 };
 
 template <bool FLASH>
-__global__ void __launch_bounds__(RB_THREADS) render_bwd(const RenderBwdParams p)
+__global__ void __launch_bounds__(RB_THREADS, WS_RB_MINB) render_bwd(const __grid_constant__ TensorMap tmap, const RenderBwdParams p)
 {
-    __shared__ __align__(128) float4 s_q0[2][RB_BATCH];
-    __shared__ __align__(128) float4 s_q1[2][RB_BATCH];
-    __shared__ __align__(128) float4 s_q2[2][RB_BATCH];
-    __shared__ __align__(8) uint64_t s_full[2];
+    __shared__ __align__(128) BwdRing sm;
 
     __shared__ uint32_t s_wmax[RB_WARPS];
     const int lane = threadIdx.x & 31;
-    const bool leader = threadIdx.x == 0;
+    const uint32_t wl = threadIdx.x >> 5;     // warp within the CTA
     // the CTAs of a tile are adjacent in launch order
     const uint32_t tile = blockIdx.x / (4 / RB_WARPS);
-    const uint32_t w = (blockIdx.x % (4 / RB_WARPS)) * RB_WARPS + (threadIdx.x >> 5);
+    const uint32_t w = (blockIdx.x % (4 / RB_WARPS)) * RB_WARPS + wl; // quadrant of the tile
+    const uint32_t cta_quads = ((1u << RB_WARPS) - 1u) << ((blockIdx.x % (4 / RB_WARPS)) * RB_WARPS);
     const int tile_y = (int)(tile / (uint32_t)p.tiles_x), tile_x = (int)(tile - (uint32_t)tile_y * p.tiles_x);
     const int wx0 = tile_x * WS_BLOCK_X + (int)(w & 1) * 8;
     const int wy0 = tile_y * WS_BLOCK_Y + (int)(w >> 1) * 8;
@@ -81,35 +85,20 @@ __global__ void __launch_bounds__(RB_THREADS) render_bwd(const RenderBwdParams p
     const uint32_t pix0 = (uint32_t)p.W * py0 + px, pix1 = pix0 + 4u * (uint32_t)p.W;
     const float pixfx = (float)px;
     const f2 npy = pk2(-(float)py0, -(float)py1);
-    const float fx0 = (float)wx0, fy0 = (float)wy0;
     const size_t HW = (size_t)p.H * p.W;
 
     const uint2 range = p.ranges[tile];
     // 1-based position of the last blended record (0 outside the image: nothing is active)
     const uint32_t last0 = in0 ? p.n_contrib[pix0] : 0u, last1 = in1 ? p.n_contrib[pix1] : 0u;
     const uint32_t wmax = __reduce_max_sync(0xffffffffu, max(last0, last1));
-    if (lane == 0) s_wmax[threadIdx.x >> 5] = wmax;
-    if (leader) {
-        mbar_init(&s_full[0], 1);
-        mbar_init(&s_full[1], 1);
-        mbar_fence_init();
-    }
-    if (RB_WARPS == 1) __syncwarp(); else __syncthreads();
+    if (lane == 0) s_wmax[wl] = wmax;
+    sm.init();
     uint32_t bmax = 0;
 #pragma unroll
     for (int k = 0; k < RB_WARPS; k++) bmax = max(bmax, s_wmax[k]);
     const int n = (int)min(bmax, range.y - range.x); // records [0, n) matter to this CTA
-    const int nb = (n + RB_BATCH - 1) / RB_BATCH;
-
-    auto issue = [&](int b, int s) {
-        const int cnt = min(RB_BATCH, n - b * RB_BATCH);
-        const uint32_t bytes = (uint32_t)cnt * 16u;
-        const size_t off = (size_t)range.x + (size_t)b * RB_BATCH;
-        mbar_expect_tx(&s_full[s], 3u * bytes);
-        tma_load_1d(&s_q0[s][0], p.q0 + off, bytes, &s_full[s]);
-        tma_load_1d(&s_q1[s][0], p.q1 + off, bytes, &s_full[s]);
-        tma_load_1d(&s_q2[s][0], p.q2 + off, bytes, &s_full[s]);
-    };
+    const int nb = (n + BwdRing::BATCH - 1) / BwdRing::BATCH;
+    const uint32_t *__restrict__ vals = p.vals + range.x;
 
     // per-pixel constants, DGR backward.cu:461-496 (lo = pixel 0, hi = pixel 1)
     const float Tf0 = in0 ? (1.0f - p.out_alpha[pix0]) : 0.0f, Tf1 = in1 ? (1.0f - p.out_alpha[pix1]) : 0.0f;
@@ -138,29 +127,47 @@ __global__ void __launch_bounds__(RB_THREADS) render_bwd(const RenderBwdParams p
     // alpha_j T_j (c_j . dL_dC + depth_j dL_dD + dL_dA)
     float Ta = Tf0, Tb = Tf1, Ra = 0.0f, Rb = 0.0f;
 
-    if (nb > 0 && leader) issue(nb - 1, 0);
+    // walking back to front: step `it` blends batch nb-1-it.  Ring prologue: steps 0 .. NSTAGE-2 requested,
+    // the value of step NSTAGE-1 in flight
+    uint32_t nv;
+    {
+        uint32_t pv[RB_NSTAGE - 1];
+#pragma unroll
+        for (int k = 0; k < RB_NSTAGE - 1; k++) pv[k] = BwdRing::load(vals, n, nb, nb - 1 - k, wl, lane);
+        nv = BwdRing::load(vals, n, nb, nb - RB_NSTAGE, wl, lane);
+#pragma unroll
+        for (int k = 0; k < RB_NSTAGE - 1; k++)
+            if (k < nb) sm.issue(&tmap, k, nb - 1 - k, pv[k], cta_quads, wl, lane);
+    }
     for (int it = 0; it < nb; it++) {
-        const int b = nb - 1 - it;
-        const int s = it & 1;
-        const int cnt = min(RB_BATCH, n - b * RB_BATCH);
-        if (it + 1 < nb && leader) issue(b - 1, (it + 1) & 1);
-        mbar_wait(&s_full[s], (uint32_t)((it >> 1) & 1));
+        const int s = it % RB_NSTAGE;
+        // slot (it-1) % NSTAGE was released by the barrier at the end of step it-1
+        if (it + RB_NSTAGE - 1 < nb)
+            sm.issue(&tmap, (it + RB_NSTAGE - 1) % RB_NSTAGE, nb - it - RB_NSTAGE, nv, cta_quads, wl, lane);
+        nv = BwdRing::load(vals, n, nb, nb - 1 - it - RB_NSTAGE, wl, lane);
+        sm.wait(it);
 
-        for (int c0 = ((cnt - 1) >> 5) << 5; c0 >= 0; c0 -= 32) {
-            const int r = c0 + lane;
+#pragma unroll 1
+        for (int seg = RB_WARPS - 1; seg >= 0; seg--) {
+          const int cnt = (int)sm.cnt[s][seg];
+          const int sbase = seg * ST_SEG;
+          {
             bool hit = false;
-            if (r < cnt && (uint32_t)(b * RB_BATCH + r) < wmax)
-                hit = rect_hit(s_q0[s][r], s_q1[s][r], fx0, fy0, 7.0f, 7.0f);
+            if (lane < cnt) {
+                const uint2 mt = sm.meta[s][sbase + lane];
+                hit = ((mt.x >> (WS_ID_BITS + w)) & 1u) != 0u && mt.y < wmax;
+            }
             uint32_t m = __ballot_sync(0xffffffffu, hit);
             while (m) {
                 const int j = 31 - __clz(m);
                 m &= ~(1u << j);
-                const int rr = c0 + j;
-                const uint32_t pos0 = (uint32_t)(b * RB_BATCH + rr);
-                const float4 a = s_q0[s][rr];
-                const float4 q = s_q1[s][rr];
-                const float4 c = s_q2[s][rr];
-                const uint32_t gid = __float_as_uint(c.w);
+                const int rr = sbase + j;
+                const uint2 meta = sm.meta[s][rr];
+                const uint32_t pos0 = meta.y;
+                const float4 a = sm.rec[s][rr].a;
+                const float4 q = sm.rec[s][rr].b;
+                const float4 c = sm.rec[s][rr].c;
+                const uint32_t gid = meta.x & WS_ID_MASK;
                 bool k0 = pos0 < last0, k1 = pos0 < last1; // backward.cu:516-518
                 if (FLASH) {
                     if (p.unique_label != nullptr) {
@@ -247,18 +254,26 @@ __global__ void __launch_bounds__(RB_THREADS) render_bwd(const RenderBwdParams p
                     else if ((lane & 15) == 1) atomicAdd(p.acc + (size_t)gid * 12 + 8 + (lane >> 4), e0);
                 }
             }
+          }
         }
-        if (RB_WARPS == 1) __syncwarp(); else __syncthreads(); // stage s is free to be refilled
+        __syncthreads(); // stage s is free to be refilled
     }
 }
 
-int launch_render_bwd(const ws_view *v, int P, GeomState &gs, BinningState &bs, ImageState &is,
+int launch_render_bwd(const ws_view *v, int P, GeomState &gs, const uint32_t *vals, ImageState &is,
                       const float *out_alpha, const float *dL_dcolor, const float *dL_ddepth,
                       const float *dL_dalpha, const ws_flash *fl, cudaStream_t st)
 {
+    if ((uint32_t)P > WS_ID_MASK) {
+        set_error("render: %d Gaussians exceed the 2^%u - 1 ids a sorted value can hold", P, WS_ID_BITS);
+        return WS_E_UNSUPPORTED;
+    }
+    TensorMap tm;
+    int rc = make_grec_tensor_map(&tm, gs.grec, P);
+    if (rc != WS_OK) return rc;
     WS_CUDA_CHECK(cudaMemsetAsync(gs.acc, 0, (size_t)P * 12 * sizeof(float), st));
     RenderBwdParams p;
-    p.ranges = is.ranges; p.q0 = bs.q0; p.q1 = bs.q1; p.q2 = bs.q2;
+    p.ranges = is.ranges; p.vals = vals;
     p.W = v->image_width; p.H = v->image_height;
     p.bg = v->bg; p.out_alpha = out_alpha; p.n_contrib = is.n_contrib;
     p.dL_dcolor = dL_dcolor; p.dL_ddepth = dL_ddepth; p.dL_dalpha = dL_dalpha;
@@ -268,9 +283,9 @@ int launch_render_bwd(const ws_view *v, int P, GeomState &gs, BinningState &bs, 
     p.tiles_x = (p.W + WS_BLOCK_X - 1) / WS_BLOCK_X;
     const unsigned grid = (unsigned)(4 / RB_WARPS) * (unsigned)p.tiles_x * (unsigned)((p.H + WS_BLOCK_Y - 1) / WS_BLOCK_Y);
     if (fl && fl->unique_label)
-        render_bwd<true><<<grid, RB_THREADS, 0, st>>>(p);
+        render_bwd<true><<<grid, RB_THREADS, 0, st>>>(tm, p);
     else
-        render_bwd<false><<<grid, RB_THREADS, 0, st>>>(p);
+        render_bwd<false><<<grid, RB_THREADS, 0, st>>>(tm, p);
     WS_LAUNCH_CHECK(st, v->debug);
     return WS_OK;
 }

@@ -10,7 +10,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 # WHEATSPLAT_LIB: another build of the same library (A/B timing of kernel variants, tools/ab.sh)
 LIB_PATH = os.environ.get("WHEATSPLAT_LIB") or os.path.join(_HERE, "libwheatsplat.so")
 
-WS_ABI_VERSION = 2
+WS_ABI_VERSION = 3
 
 # every symbol include/wheatsplat.h declares (tests check the library exports all of them)
 SYMBOLS = [
@@ -139,7 +139,7 @@ def load():
     lib.ws_objeval_bin.argtypes = [C.POINTER(WsView), C.POINTER(WsGaussians), C.POINTER(WsObjSets), vp, vp, vp, sz,
                                    vp, sz, i64, vp]
     lib.ws_objeval_render.restype = C.c_int
-    lib.ws_objeval_render.argtypes = [C.POINTER(WsView), C.POINTER(WsObjSets), vp, vp, sz, i64, i64, vp, sz, vp, vp]
+    lib.ws_objeval_render.argtypes = [C.POINTER(WsView), C.POINTER(WsObjSets), i32, vp, vp, vp, sz, i64, i64, vp, sz, vp, vp]
     lib.ws_allreduce_sum_f32.restype = C.c_int
     lib.ws_allreduce_sum_f32.argtypes = [i32, i32, i64, vp, C.POINTER(vp), i32, vp]
     lib.ws_allreduce_tune.restype = C.c_int
@@ -173,7 +173,7 @@ def load():
     lib.ws_prof_stage_name.restype = C.c_char_p
     lib.ws_prof_stage_name.argtypes = [i32]
     lib.ws_debug_count_pairs.restype = C.c_int
-    lib.ws_debug_count_pairs.argtypes = [i32, i32, vp, vp, i64, vp, vp]
+    lib.ws_debug_count_pairs.argtypes = [i32, i32, i32, vp, vp, vp, i64, vp, vp]
     lib.ws_debug_fma_peak.restype = i64
     lib.ws_debug_fma_peak.argtypes = [i32, i32, i32, vp, vp]
     if lib.ws_abi_version() != WS_ABI_VERSION:

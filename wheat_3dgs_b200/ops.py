@@ -443,15 +443,15 @@ def prof_read():
     return {L.ws_prof_stage_name(i).decode(): (ms[i], int(calls[i])) for i in range(n)}
 
 
-def count_pairs(W, H, R, binning, image):
-    """(N_eval, N_contrib) of a finished forward (see ws_debug_count_pairs)."""
+def count_pairs(P, W, H, R, geom, binning, image):
+    """(N_eval, N_contrib, quadrant-warp pairs after the cull, instances with an empty mask) of a finished forward
+    (see ws_debug_count_pairs)."""
     L = _lib.load()
-    counts = torch.zeros((2,), dtype=torch.int64, device=image.device)
+    counts = torch.zeros((4,), dtype=torch.int64, device=image.device)
     with torch.cuda.device(image.device):
-        _lib.check(L.ws_debug_count_pairs(W, H, _ptr(binning), image.data_ptr(), int(R), counts.data_ptr(), _stream()),
-                   "ws_debug_count_pairs")
-    c = counts.cpu().tolist()
-    return int(c[0]), int(c[1])
+        _lib.check(L.ws_debug_count_pairs(int(P), W, H, geom.data_ptr(), _ptr(binning), image.data_ptr(), int(R),
+                                          counts.data_ptr(), _stream()), "ws_debug_count_pairs")
+    return tuple(int(x) for x in counts.cpu().tolist())
 
 
 def fma_peak(packed, device=None, iters=4096, ctas=148 * 8, repeats=5):

@@ -114,7 +114,7 @@ def eval_obj_labels_tensors(sets, raster_settings, means3D, opacities, shs=None,
                                         geom.data_ptr(), _ops._ptr(binning), binning.numel(), scratch.data_ptr(),
                                         scratch.numel(), R, st), "ws_objeval_bin")
         job_out = torch.empty((max(J, 1) * 512,), dtype=torch.float32, device=dev)
-        _lib.check(L.ws_objeval_render(C.byref(call.view), C.byref(ws), _ops._ptr(binning), scratch.data_ptr(),
+        _lib.check(L.ws_objeval_render(C.byref(call.view), C.byref(ws), P, geom.data_ptr(), _ops._ptr(binning), scratch.data_ptr(),
                                        scratch.numel(), R, J, job_out.data_ptr(), job_out.numel() * 4,
                                        pred.data_ptr(), st), "ws_objeval_render")
     eval_obj_labels_tensors.last_counts = (R, J)
