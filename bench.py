@@ -631,7 +631,6 @@ def run_train(args, job, workload, steps, warmup, with_e2e=True):
         parity = {"checked": True, "against": "reference stack losses of the first iterations (tests/golden/fullsize.json)",
                   "losses": mine, "reference_losses": gold["losses"], "max_rel_err": max(rel), "ok": bool(max(rel) < 1e-4)}
         del chk
-        torch.cuda.empty_cache()
     elif gold is not None:
         parity = {"checked": False, "why": "the loss golden is single-GPU semantics (one view per step); checked at N=1"}
 
@@ -661,7 +660,6 @@ def run_train(args, job, workload, steps, warmup, with_e2e=True):
         out["ms_e2e"] = job.timed(e2e_step, steps, warmup, after=res.flush)
         out["h2d"], out["d2h"] = 3 * H * W * 4 + 35 * 4, 4
     del tr
-    torch.cuda.empty_cache()
     return out
 
 

@@ -98,7 +98,7 @@ class Trainer:
             self.sharded.step()
             for q in p.values():
                 q.grad = None
-            return loss
+            return loss.detach()
         if self.reduce is not None:
             # the statistics above stay per rank (summed only when densification reads them,
             # dist.allreduce_densify_stats); the parameter gradients are the bucket's slices, summed in place
@@ -109,4 +109,4 @@ class Trainer:
                 p[n].grad = b[self._off[n]:self._off[n] + numel].view(self._shape[n])
         self.opt.step()
         self.opt.zero_grad(set_to_none=True)
-        return loss
+        return loss.detach()
