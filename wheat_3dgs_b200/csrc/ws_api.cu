@@ -78,13 +78,28 @@ cudaEvent_t total_event()
     return ev[dev];
 }
 
-// pinned landing word for num_rendered: a D2H copy into pageable memory blocks the host until
-// the stream has drained, a copy into pinned memory is asynchronous
+// pinned landing words for device -> host counts (a D2H copy into pageable memory blocks the host until the stream
+// has drained, a copy into pinned memory is asynchronous).  Mapped into the device's address space as well (same
+// pointer under unified addressing): words 8..9 are the mailbox the scan kernel writes num_rendered into directly.
 uint32_t *total_host()
 {
     static thread_local uint32_t *p = nullptr;
-    if (!p && cudaHostAlloc((void **)&p, 64, cudaHostAllocDefault) != cudaSuccess) p = nullptr;
+    if (!p) {
+        if (cudaHostAlloc((void **)&p, 64, cudaHostAllocMapped | cudaHostAllocPortable) != cudaSuccess) p = nullptr;
+        else memset(p, 0, 64);
+    }
     return p;
+}
+
+// per-thread, per-device non-blocking stream for the mailbox store
+cudaStream_t side_stream()
+{
+    static thread_local cudaStream_t ss[16] = {};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    dev &= 15;
+    if (!ss[dev] && cudaStreamCreateWithFlags(&ss[dev], cudaStreamNonBlocking) != cudaSuccess) ss[dev] = nullptr;
+    return ss[dev];
 }
 
 // DGR rasterizer_impl.cu:35-50
@@ -220,23 +235,51 @@ extern "C" int64_t ws_forward_prepare(const ws_view *view, const ws_gaussians *g
     GeomState gs = GeomState::from((char *)geom, (size_t)g->P);
     { ProfScope ps(0, st); rc = launch_preprocess(view, g, radii, gs, fl, st); }
     if (rc != WS_OK) return rc;
-    { ProfScope ps(1, st); rc = launch_scan_blocks(g->P, gs, st, view->debug != 0); }
-    if (rc != WS_OK) return rc;
     uint32_t *th = total_host();
     if (!th) { set_error("ws_forward_prepare: cudaHostAlloc failed"); return WS_E_CUDA; }
-    WS_CUDA_CHECK(cudaMemcpyAsync(th, gs.total, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+    // num_rendered reaches the host through a mailbox in mapped pinned memory: a one-thread kernel on a side stream,
+    // behind the scan, stores {sequence number, total} as one 8-byte word and the host spins on it.  A D2H copy in
+    // the main stream held back everything queued behind it (25 us on the copy engine next to a 38 MB input upload,
+    // plus the engine hand-over); this way the depth sort, which needs nothing from the host, starts right behind
+    // the scan and runs while the host learns R, sizes the binning scratch and queues the rest of the forward (the
+    // reference idles the GPU there, rasterizer_impl.cu:282).
+    static thread_local uint32_t seq_counter = 0;
+    const uint32_t seq = ++seq_counter ? seq_counter : ++seq_counter;
+    volatile unsigned long long *mb = (volatile unsigned long long *)(th + 8);
+    { ProfScope ps(1, st); rc = launch_scan_blocks(g->P, gs, st, view->debug != 0); }
+    if (rc != WS_OK) return rc;
+    cudaEvent_t ev = total_event();
+    cudaStream_t side = side_stream();
+    if (!side) { set_error("ws_forward_prepare: cudaStreamCreate failed"); return WS_E_CUDA; }
+    WS_CUDA_CHECK(cudaEventRecord(ev, st));
+    WS_CUDA_CHECK(cudaStreamWaitEvent(side, ev, 0));
+    rc = launch_post_total(gs.total, (unsigned long long *)(th + 8), seq, side);
+    if (rc != WS_OK) return rc;
+    WS_CUDA_CHECK(cudaEventRecord(ev, side));
     if (!binning_keys64()) {
-        // the depth sort needs nothing from the host: it runs while the host waits for `total`
-        // and sizes the binning scratch (the reference idles the GPU there, rasterizer_impl.cu:282)
-        cudaEvent_t ev = total_event();
-        WS_CUDA_CHECK(cudaEventRecord(ev, st));
         { ProfScope ps(3, st); rc = launch_depth_sort(g->P, gs, st, view->debug != 0); }
         if (rc != WS_OK) return rc;
-        WS_CUDA_CHECK(cudaEventSynchronize(ev));
-    } else {
-        WS_CUDA_CHECK(cudaStreamSynchronize(st));
     }
-    return (int64_t)*th;
+    unsigned long long word;
+    for (uint32_t spins = 1;; spins++) {
+        word = *mb;
+        if ((uint32_t)(word >> 32) == seq) break;
+        __builtin_ia32_pause();
+        if ((spins & 1023u) == 0) {   // the kernel is gone (finished without our sequence number, or failed)?
+            cudaError_t q = cudaEventQuery(ev);
+            if (q == cudaSuccess) {
+                word = *mb;
+                if ((uint32_t)(word >> 32) == seq) break;
+                set_error("ws_forward_prepare: the scan finished without delivering num_rendered");
+                return WS_E_CUDA;
+            }
+            if (q != cudaErrorNotReady) {
+                set_error("ws_forward_prepare: %s while waiting for num_rendered", cudaGetErrorString(q));
+                return WS_E_CUDA;
+            }
+        }
+    }
+    return (int64_t)(uint32_t)word;
 }
 
 extern "C" int ws_forward_render(const ws_view *view, const ws_gaussians *g, const int32_t *radii, void *geom,
@@ -270,6 +313,7 @@ extern "C" int ws_forward_render(const ws_view *view, const ws_gaussians *g, con
     BinningState bs = BinningState::from((char *)binning, R);
     uint64_t *keys = nullptr;
     uint32_t *tkeys = nullptr, *vals = nullptr;
+    bool ranges_cleared = false;
     if (R > 0 && binning_keys64()) {
         { ProfScope ps(2, st); rc = launch_emit_keys(g->P, W, H, radii, gs, bs.keys_a, bs.vals_a, st, debug); }
         if (rc != WS_OK) return rc;
@@ -277,13 +321,17 @@ extern "C" int ws_forward_render(const ws_view *view, const ws_gaussians *g, con
         { ProfScope ps(3, st); rc = launch_sort_pairs(R, bs.keys_a, bs.keys_b, bs.vals_a, bs.vals_b, end_bit, bs.sort, st, debug, &keys, &vals); }
         if (rc != WS_OK) return rc;
     } else if (R > 0) {
-        { ProfScope ps(2, st); rc = launch_emit_tiles_ordered(g->P, W, H, radii, gs, bs.tkeys_a, bs.vals_a, st, debug); }
-        if (rc != WS_OK) return rc;
+        // the emit pass counts the tile keys' digits while it writes them: the sort needs no pass of its own for that
         const int end_bit = (int)get_higher_msb((uint32_t)T);
-        { ProfScope ps(3, st); rc = launch_sort_pairs32(R, bs.tkeys_a, bs.tkeys_b, bs.vals_a, bs.vals_b, end_bit, bs.sort, st, debug, &tkeys, &vals); }
+        // (the stage's first kernel also clears the sort's scratch words and the tile ranges)
+        { ProfScope ps(2, st); rc = launch_emit_tiles_ordered(g->P, W, H, radii, gs, bs.tkeys_a, bs.vals_a, st, debug, bs.sort.hist, (end_bit + 7) / 8,
+                                                              bs.sort.hist, sort_scratch_words(R, end_bit), (uint32_t *)is.ranges, (size_t)T * 2); }
+        ranges_cleared = true;
+        if (rc != WS_OK) return rc;
+        { ProfScope ps(3, st); rc = launch_sort_pairs32(R, bs.tkeys_a, bs.tkeys_b, bs.vals_a, bs.vals_b, end_bit, bs.sort, st, debug, &tkeys, &vals, true); }
         if (rc != WS_OK) return rc;
     }
-    { ProfScope ps(4, st); rc = launch_identify_ranges(R, T, keys, tkeys, is.ranges, st, debug); }
+    { ProfScope ps(4, st); rc = launch_identify_ranges(R, T, keys, tkeys, is.ranges, st, debug, ranges_cleared); }
     if (rc != WS_OK) return rc;
     { ProfScope ps(5, st); rc = launch_render_fwd(view, g->P, gs, vals, is, out_color, out_depth, out_alpha, fl, st); }
     return rc;

@@ -32,12 +32,43 @@ __global__ void __launch_bounds__(256) identify_ranges(size_t R, const K *__rest
     if (idx == R - 1) ranges[currtile].y = (uint32_t)R;
 }
 
-int launch_identify_ranges(size_t R, int T, const uint64_t *keys, const uint32_t *tkeys, uint2 *ranges,
-                           cudaStream_t st, bool debug)
+// 32-bit tile keys, four per thread (one 16-byte load + the key in front of them)
+__global__ void __launch_bounds__(256) identify_ranges4(size_t R, const uint32_t *__restrict__ keys, uint2 *__restrict__ ranges)
 {
-    WS_CUDA_CHECK(cudaMemsetAsync(ranges, 0, (size_t)T * sizeof(uint2), st));
+    const size_t base = 4 * ((size_t)blockIdx.x * blockDim.x + threadIdx.x);
+    if (base >= R) return;
+    uint32_t k[4];
+    if (base + 3 < R) {
+        const uint4 v = *reinterpret_cast<const uint4 *>(keys + base);
+        k[0] = v.x; k[1] = v.y; k[2] = v.z; k[3] = v.w;
+    } else {
+#pragma unroll
+        for (int j = 0; j < 4; j++) k[j] = base + j < R ? keys[base + j] : 0u;
+    }
+    uint32_t prev = base ? keys[base - 1] : 0u;
+    if (base == 0) ranges[k[0]].x = 0;
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+        const size_t idx = base + j;
+        if (idx < R) {
+            if (idx != 0 && k[j] != prev) {
+                ranges[prev].y = (uint32_t)idx;
+                ranges[k[j]].x = (uint32_t)idx;
+            }
+            if (idx == R - 1) ranges[k[j]].y = (uint32_t)R;
+            prev = k[j];
+        }
+    }
+}
+
+int launch_identify_ranges(size_t R, int T, const uint64_t *keys, const uint32_t *tkeys, uint2 *ranges,
+                           cudaStream_t st, bool debug, bool ranges_cleared)
+{
+    if (!ranges_cleared) WS_CUDA_CHECK(cudaMemsetAsync(ranges, 0, (size_t)T * sizeof(uint2), st));
     if (R == 0) return WS_OK;
-    if (tkeys)
+    if (tkeys && ((uintptr_t)tkeys & 15) == 0)
+        identify_ranges4<<<(unsigned)((R + 1023) / 1024), 256, 0, st>>>(R, tkeys, ranges);
+    else if (tkeys)
         identify_ranges<uint32_t><<<(unsigned)((R + 255) / 256), 256, 0, st>>>(R, tkeys, ranges);
     else
         identify_ranges<uint64_t><<<(unsigned)((R + 255) / 256), 256, 0, st>>>(R, keys, ranges);

@@ -376,6 +376,20 @@ __global__ void __launch_bounds__(1024) scan_block_sums(int nb, const uint32_t *
     if (tid == 0) total[0] = s_carry;
 }
 
+// num_rendered for the host: one 8-byte store {seq, total} into a pinned, device-mapped mailbox the host spins on
+// (ws_forward_prepare).  Runs on a side stream behind the scan, so the store's trip over PCIe holds nothing up.
+__global__ void post_total(const uint32_t *__restrict__ total, unsigned long long *mailbox, uint32_t seq)
+{
+    *(volatile unsigned long long *)mailbox = ((unsigned long long)seq << 32) | (unsigned long long)total[0];
+}
+
+int launch_post_total(const uint32_t *total, unsigned long long *mailbox, uint32_t seq, cudaStream_t side)
+{
+    post_total<<<1, 1, 0, side>>>(total, mailbox, seq);
+    WS_LAUNCH_CHECK(side, false);
+    return WS_OK;
+}
+
 int launch_scan_u32(int nb, const uint32_t *sums, uint32_t *offsets, uint32_t *total, cudaStream_t st, bool debug)
 {
     scan_block_sums<<<1, 1024, 0, st>>>(nb, sums, offsets, total);
@@ -490,12 +504,21 @@ int launch_depth_sort(int P, GeomState &gs, cudaStream_t st, bool debug)
 const uint32_t *depth_order(const GeomState &gs) { return gs.dvals_a; }
 
 // tiles_touched summed over blocks of 256 Gaussians taken in depth order
+// Also clears up to two word arrays for the stages behind it (the tile sort's histograms / status words and the tile
+// ranges): two memset launches less between the host learning R and the blend kernel.
 __global__ void __launch_bounds__(WS_PRE_THREADS) ordered_block_sums(int P, const uint32_t *__restrict__ order,
                                                                      const uint32_t *__restrict__ tiles_touched,
-                                                                     uint32_t *__restrict__ block_sums)
+                                                                     uint32_t *__restrict__ block_sums,
+                                                                     uint32_t *__restrict__ zero_a, size_t na,
+                                                                     uint32_t *__restrict__ zero_b, size_t nb_words)
 {
     __shared__ uint32_t s_w[WS_PRE_THREADS / 32];
     const int i = blockIdx.x * WS_PRE_THREADS + threadIdx.x;
+    {
+        const size_t stride = (size_t)gridDim.x * WS_PRE_THREADS;
+        for (size_t j = (size_t)i; j < na; j += stride) zero_a[j] = 0u;
+        for (size_t j = (size_t)i; j < nb_words; j += stride) zero_b[j] = 0u;
+    }
     uint32_t s = i < P ? tiles_touched[order[i]] : 0u;
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
@@ -517,10 +540,16 @@ __global__ void __launch_bounds__(WS_PRE_THREADS) emit_tiles_ordered(int P, int 
                                                                      const uint32_t *__restrict__ tiles_touched,
                                                                      const uint32_t *__restrict__ block_offsets,
                                                                      uint32_t *__restrict__ tkeys,
-                                                                     uint32_t *__restrict__ vals)
+                                                                     uint32_t *__restrict__ vals,
+                                                                     uint32_t *__restrict__ hist, int npass)
 {
     __shared__ uint32_t s_w[WS_PRE_THREADS / 32];
+    // digit counts of the keys this CTA emits, all passes of the tile sort (pass p = key bits [8p, 8p+8)): the sort
+    // needs them before its first pass and would otherwise read every key once more to get them
+    __shared__ uint32_t s_hist[4 * 256];
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+    if (hist)
+        for (int j = tid; j < npass * 256; j += WS_PRE_THREADS) s_hist[j] = 0;
     const int i = blockIdx.x * WS_PRE_THREADS + tid;
     uint32_t tt = 0, rminx = 0, rminy = 0, width = 1, gid = 0;
     float4 ga = make_float4(0.f, 0.f, 0.f, 0.f), gb = ga;
@@ -563,30 +592,58 @@ __global__ void __launch_bounds__(WS_PRE_THREADS) emit_tiles_ordered(int P, int 
         const uint32_t o_w = __shfl_sync(0xffffffffu, width, j);
         const uint32_t o_id = __shfl_sync(0xffffffffu, gid, j);
         const QuadTest oq = shfl_quad_test(qt, j);
+        uint32_t key = 0xffffffffu;
         if (k < warp_total) {
             const uint32_t local = k - o_excl;
             const uint32_t ty = local / o_w, tx = local - ty * o_w;
-            tkeys[(size_t)warp_base + k] = (o_miny + ty) * (uint32_t)gx + (o_minx + tx);
+            key = (o_miny + ty) * (uint32_t)gx + (o_minx + tx);
+            tkeys[(size_t)warp_base + k] = key;
             // which 8x8 quadrants of this tile the Gaussian can reach: the blend kernels' sub-tile cull, paid
             // once per instance here instead of once per (warp, record) in every blend pass
             const uint32_t qm = quad_mask(oq, (float)((o_minx + tx) * WS_BLOCK_X), (float)((o_miny + ty) * WS_BLOCK_Y));
             vals[(size_t)warp_base + k] = o_id | (qm << WS_ID_BITS);
         }
+        if (hist) {
+            // pass 0: neighbouring lanes hold neighbouring tiles, different bins.  Higher passes: runs of equal
+            // digits (a Gaussian's row of tiles), one add per run by its first lane.
+            if (k < warp_total) atomicAdd(&s_hist[key & 255u], 1u);
+            for (int p = 1; p < npass; p++) {
+                const uint32_t d = key >> (8 * p);   // 0xffffff.. for idle lanes: never equal to a live digit
+                const uint32_t up = __shfl_up_sync(0xffffffffu, d, 1);
+                const bool head = lane == 0 || d != up;
+                const uint32_t heads = __ballot_sync(0xffffffffu, head);
+                if (head && k < warp_total) {
+                    const uint32_t after = heads & ~((2u << lane) - 1u); // heads strictly above this lane
+                    const uint32_t next = after ? (uint32_t)__ffs(after) - 1u : 32u;
+                    atomicAdd(&s_hist[p * 256 + (d & 255u)], next - (uint32_t)lane);
+                }
+            }
+        }
+    }
+    if (hist) {
+        __syncthreads();
+        for (int j = tid; j < npass * 256; j += WS_PRE_THREADS) {
+            const uint32_t c = s_hist[j];
+            if (c) atomicAdd(hist + j, c);
+        }
     }
 }
 
 int launch_emit_tiles_ordered(int P, int W, int H, const int32_t *radii, GeomState &gs, uint32_t *tkeys,
-                              uint32_t *vals, cudaStream_t st, bool debug)
+                              uint32_t *vals, cudaStream_t st, bool debug, uint32_t *hist, int npass,
+                              uint32_t *zero_a, size_t zero_a_words, uint32_t *zero_b, size_t zero_b_words)
 {
+    if (npass > 4) hist = nullptr; // (more than 2^32 tiles: not reachable; the sort then counts for itself)
     const int gx = (W + WS_BLOCK_X - 1) / WS_BLOCK_X, gy = (H + WS_BLOCK_Y - 1) / WS_BLOCK_Y;
     const int nb = (P + WS_PRE_THREADS - 1) / WS_PRE_THREADS;
     const uint32_t *order = depth_order(gs);
-    ordered_block_sums<<<nb, WS_PRE_THREADS, 0, st>>>(P, order, gs.tiles_touched, gs.block_sums);
+    ordered_block_sums<<<nb, WS_PRE_THREADS, 0, st>>>(P, order, gs.tiles_touched, gs.block_sums, zero_a, zero_a_words,
+                                                      zero_b, zero_b_words);
     WS_LAUNCH_CHECK(st, debug);
     scan_block_sums<<<1, 1024, 0, st>>>(nb, gs.block_sums, gs.block_offsets, gs.total + 1);
     WS_LAUNCH_CHECK(st, debug);
     emit_tiles_ordered<<<nb, WS_PRE_THREADS, 0, st>>>(P, gx, gy, order, radii, gs.grec, gs.tiles_touched,
-                                                      gs.block_offsets, tkeys, vals);
+                                                      gs.block_offsets, tkeys, vals, hist, npass);
     WS_LAUNCH_CHECK(st, debug);
     return WS_OK;
 }

@@ -27,7 +27,10 @@ constexpr int RS_WARPS = RS_THREADS / 32;
 constexpr int RS_ITEMS = 12;
 constexpr int RS_TILE = RS_THREADS * RS_ITEMS; // 3072 pairs per CTA
 constexpr int RS_MAX_PASSES = 8;
-constexpr int RS_LOOK = 8;
+#ifndef WS_RS_LOOK
+#define WS_RS_LOOK 8
+#endif
+constexpr int RS_LOOK = WS_RS_LOOK; // predecessors read per look-back round trip
 
 constexpr uint32_t RS_FLAG_AGG = 1u << 30; // tile aggregate available
 constexpr uint32_t RS_FLAG_INC = 2u << 30; // inclusive prefix available
@@ -46,10 +49,11 @@ size_t sort_tiles(size_t n)
 SortScratch SortScratch::from(char *&p, size_t n)
 {
     SortScratch s;
-    s.hist = carve<uint32_t>(p, RS_MAX_PASSES * 256 + 64); // counters live right behind hist
-    s.counters = s.hist + RS_MAX_PASSES * 256;
+    // one contiguous block: [hist 8 x 256 | counters 64 | status passes x tiles x 256] (cleared by one memset)
     size_t nt = sort_tiles(n);
-    s.status = carve<uint32_t>(p, (size_t)RS_MAX_PASSES * (nt ? nt : 1) * 256);
+    s.hist = carve<uint32_t>(p, RS_MAX_PASSES * 256 + 64 + (size_t)RS_MAX_PASSES * (nt ? nt : 1) * 256);
+    s.counters = s.hist + RS_MAX_PASSES * 256;
+    s.status = s.counters + 64;
     return s;
 }
 
@@ -259,10 +263,24 @@ rs_onesweep(const K *__restrict__ keys_in, K *__restrict__ keys_out,
                                       status, s_keys, s_vals, s_whist, s_dstart, s_goff, s_w);
 }
 
+// hist + counters + status words are one contiguous carve (SortScratch::from): one memset clears them
+size_t sort_scratch_words(size_t n, int end_bit)
+{
+    const int npass = (end_bit + 7) / 8;
+    return (size_t)RS_MAX_PASSES * 256 + 64 + (size_t)npass * sort_tiles(n) * 256;
+}
+int sort_clear_scratch(size_t n, int end_bit, SortScratch &ss, cudaStream_t st)
+{
+    WS_CUDA_CHECK(cudaMemsetAsync(ss.hist, 0, sort_scratch_words(n, end_bit) * sizeof(uint32_t), st));
+    return WS_OK;
+}
+
+// have_hist: the caller cleared the scratch (sort_clear_scratch) and accumulated the per-pass digit histograms into
+// ss.hist itself (emit_tiles_ordered does, while it writes the keys): no histogram pass over the keys here
 template <typename K>
 static int sort_pairs_impl(size_t n, K *keys_in, K *keys_out, uint32_t *vals_in,
                            uint32_t *vals_out, int end_bit, SortScratch &ss, cudaStream_t st, bool debug,
-                           K **keys_final, uint32_t **vals_final)
+                           K **keys_final, uint32_t **vals_final, bool have_hist = false)
 {
     *keys_final = keys_in;
     *vals_final = vals_in;
@@ -277,12 +295,14 @@ static int sort_pairs_impl(size_t n, K *keys_in, K *keys_out, uint32_t *vals_in,
     }
     const int npass = (end_bit + 7) / 8;
     const size_t nt = sort_tiles(n);
-    WS_CUDA_CHECK(cudaMemsetAsync(ss.hist, 0, (RS_MAX_PASSES * 256 + 64) * sizeof(uint32_t), st));
-    WS_CUDA_CHECK(cudaMemsetAsync(ss.status, 0, (size_t)npass * nt * 256 * sizeof(uint32_t), st));
-    int hb = (int)((n + 256 * 16 - 1) / (256 * 16));
-    if (hb > 148 * 8) hb = 148 * 8;
-    rs_histogram<K><<<hb, 256, 0, st>>>(keys_in, n, end_bit, ss.hist);
-    WS_LAUNCH_CHECK(st, debug);
+    if (!have_hist) {
+        int rc = sort_clear_scratch(n, end_bit, ss, st);
+        if (rc != WS_OK) return rc;
+        int hb = (int)((n + 256 * 16 - 1) / (256 * 16));
+        if (hb > 148 * 8) hb = 148 * 8;
+        rs_histogram<K><<<hb, 256, 0, st>>>(keys_in, n, end_bit, ss.hist);
+        WS_LAUNCH_CHECK(st, debug);
+    }
     rs_scan_hist<<<npass, 256, 0, st>>>(ss.hist);
     WS_LAUNCH_CHECK(st, debug);
     K *ki = keys_in, *ko = keys_out;
@@ -314,10 +334,10 @@ int launch_sort_pairs(size_t n, uint64_t *keys_in, uint64_t *keys_out, uint32_t 
 
 int launch_sort_pairs32(size_t n, uint32_t *keys_in, uint32_t *keys_out, uint32_t *vals_in,
                         uint32_t *vals_out, int end_bit, SortScratch &ss, cudaStream_t st, bool debug,
-                        uint32_t **keys_final, uint32_t **vals_final)
+                        uint32_t **keys_final, uint32_t **vals_final, bool have_hist)
 {
     return sort_pairs_impl<uint32_t>(n, keys_in, keys_out, vals_in, vals_out, end_bit, ss, st, debug, keys_final,
-                                     vals_final);
+                                     vals_final, have_hist);
 }
 
 } // namespace ws

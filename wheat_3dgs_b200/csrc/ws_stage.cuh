@@ -17,7 +17,11 @@
 
 namespace ws {
 
-constexpr int ST_SEG = 64; // instances per batch (two per lane)
+#ifndef WS_ST_SEG
+#define WS_ST_SEG 64
+#endif
+constexpr int ST_SEG = WS_ST_SEG; // instances per batch: 64 (two per lane) or 32 (one per lane)
+static_assert(ST_SEG == 64 || ST_SEG == 32, "a batch is one or two values per lane");
 
 template <int NSTAGE>
 struct __align__(128) WarpRing {
@@ -42,7 +46,7 @@ struct __align__(128) WarpRing {
         uint2 v = make_uint2(0u, 0u);
         if (b >= 0 && b < nb) {
             if (i < n) v.x = __ldg(vals + i);
-            if (i + 32 < n) v.y = __ldg(vals + i + 32);
+            if (ST_SEG == 64 && i + 32 < n) v.y = __ldg(vals + i + 32);
         }
         return v;
     }
