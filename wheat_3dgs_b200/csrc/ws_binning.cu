@@ -36,6 +36,8 @@ __global__ void __launch_bounds__(256) identify_ranges(size_t R, const K *__rest
 __global__ void __launch_bounds__(256) identify_ranges4(size_t R, const uint32_t *__restrict__ keys, uint2 *__restrict__ ranges)
 {
     const size_t base = 4 * ((size_t)blockIdx.x * blockDim.x + threadIdx.x);
+    pdl_wait();
+    pdl_trigger();
     if (base >= R) return;
     uint32_t k[4];
     if (base + 3 < R) {
@@ -67,7 +69,7 @@ int launch_identify_ranges(size_t R, int T, const uint64_t *keys, const uint32_t
     if (!ranges_cleared) WS_CUDA_CHECK(cudaMemsetAsync(ranges, 0, (size_t)T * sizeof(uint2), st));
     if (R == 0) return WS_OK;
     if (tkeys && ((uintptr_t)tkeys & 15) == 0)
-        identify_ranges4<<<(unsigned)((R + 1023) / 1024), 256, 0, st>>>(R, tkeys, ranges);
+        WS_CUDA_CHECK(launch_pdl(identify_ranges4, dim3((unsigned)((R + 1023) / 1024)), dim3(256), 0, st, R, tkeys, ranges));
     else if (tkeys)
         identify_ranges<uint32_t><<<(unsigned)((R + 255) / 256), 256, 0, st>>>(R, tkeys, ranges);
     else

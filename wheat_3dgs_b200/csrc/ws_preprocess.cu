@@ -343,6 +343,8 @@ __global__ void __launch_bounds__(1024) scan_block_sums(int nb, const uint32_t *
     __shared__ uint32_t s_w[32];
     __shared__ uint32_t s_carry;
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+    pdl_wait();
+    pdl_trigger();
     if (tid == 0) s_carry = 0;
     __syncthreads();
     for (int c0 = 0; c0 < nb; c0 += 1024) {
@@ -514,6 +516,8 @@ __global__ void __launch_bounds__(WS_PRE_THREADS) ordered_block_sums(int P, cons
 {
     __shared__ uint32_t s_w[WS_PRE_THREADS / 32];
     const int i = blockIdx.x * WS_PRE_THREADS + threadIdx.x;
+    pdl_wait();
+    pdl_trigger();
     {
         const size_t stride = (size_t)gridDim.x * WS_PRE_THREADS;
         for (size_t j = (size_t)i; j < na; j += stride) zero_a[j] = 0u;
@@ -550,6 +554,8 @@ __global__ void __launch_bounds__(WS_PRE_THREADS) emit_tiles_ordered(int P, int 
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
     if (hist)
         for (int j = tid; j < npass * 256; j += WS_PRE_THREADS) s_hist[j] = 0;
+    pdl_wait();
+    pdl_trigger();
     const int i = blockIdx.x * WS_PRE_THREADS + tid;
     uint32_t tt = 0, rminx = 0, rminy = 0, width = 1, gid = 0;
     float4 ga = make_float4(0.f, 0.f, 0.f, 0.f), gb = ga;
@@ -637,13 +643,14 @@ int launch_emit_tiles_ordered(int P, int W, int H, const int32_t *radii, GeomSta
     const int gx = (W + WS_BLOCK_X - 1) / WS_BLOCK_X, gy = (H + WS_BLOCK_Y - 1) / WS_BLOCK_Y;
     const int nb = (P + WS_PRE_THREADS - 1) / WS_PRE_THREADS;
     const uint32_t *order = depth_order(gs);
-    ordered_block_sums<<<nb, WS_PRE_THREADS, 0, st>>>(P, order, gs.tiles_touched, gs.block_sums, zero_a, zero_a_words,
-                                                      zero_b, zero_b_words);
+    WS_CUDA_CHECK(launch_pdl(ordered_block_sums, dim3(nb), dim3(WS_PRE_THREADS), 0, st, P, order, gs.tiles_touched,
+                             gs.block_sums, zero_a, zero_a_words, zero_b, zero_b_words));
     WS_LAUNCH_CHECK(st, debug);
-    scan_block_sums<<<1, 1024, 0, st>>>(nb, gs.block_sums, gs.block_offsets, gs.total + 1);
+    WS_CUDA_CHECK(launch_pdl(scan_block_sums, dim3(1), dim3(1024), 0, st, nb, gs.block_sums, gs.block_offsets,
+                             gs.total + 1));
     WS_LAUNCH_CHECK(st, debug);
-    emit_tiles_ordered<<<nb, WS_PRE_THREADS, 0, st>>>(P, gx, gy, order, radii, gs.grec, gs.tiles_touched,
-                                                      gs.block_offsets, tkeys, vals, hist, npass);
+    WS_CUDA_CHECK(launch_pdl(emit_tiles_ordered, dim3(nb), dim3(WS_PRE_THREADS), 0, st, P, gx, gy, order, radii, gs.grec,
+                             gs.tiles_touched, gs.block_offsets, tkeys, vals, hist, npass));
     WS_LAUNCH_CHECK(st, debug);
     return WS_OK;
 }

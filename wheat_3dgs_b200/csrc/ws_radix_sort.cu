@@ -104,6 +104,8 @@ __device__ __forceinline__ uint32_t block_excl_scan_256(uint32_t v, uint32_t *s_
 __global__ void __launch_bounds__(256) rs_scan_hist(uint32_t *__restrict__ hist)
 {
     __shared__ uint32_t s_w[RS_WARPS];
+    pdl_wait();
+    pdl_trigger();
     uint32_t *h = hist + blockIdx.x * 256;
     const uint32_t v = h[threadIdx.x];
     h[threadIdx.x] = block_excl_scan_256(v, s_w);
@@ -250,6 +252,10 @@ rs_onesweep(const K *__restrict__ keys_in, K *__restrict__ keys_out,
     if (tid == 0) s_tile = atomicAdd(counter, 1u); // ticket: predecessors are always resident
 #pragma unroll
     for (int k = 0; k < RS_WARPS; k++) s_whist[k][tid] = 0;
+    // (the ticket counter and status words of this pass were cleared before the sort's first kernel: nothing above
+    // depends on the previous pass, whose keys are read from here on)
+    pdl_wait();
+    pdl_trigger();
     __syncthreads();
     const uint32_t tile = s_tile;
     const size_t base = (size_t)tile * TILE;
@@ -303,18 +309,19 @@ static int sort_pairs_impl(size_t n, K *keys_in, K *keys_out, uint32_t *vals_in,
         rs_histogram<K><<<hb, 256, 0, st>>>(keys_in, n, end_bit, ss.hist);
         WS_LAUNCH_CHECK(st, debug);
     }
-    rs_scan_hist<<<npass, 256, 0, st>>>(ss.hist);
+    WS_CUDA_CHECK(launch_pdl(rs_scan_hist, dim3(npass), dim3(256), 0, st, ss.hist));
     WS_LAUNCH_CHECK(st, debug);
     K *ki = keys_in, *ko = keys_out;
     uint32_t *vi = vals_in, *vo = vals_out;
     for (int p = 0; p < npass; p++) {
         const int bits = end_bit - 8 * p < 8 ? end_bit - 8 * p : 8;
         if (sort_items(n) == 4)
-            rs_onesweep<K, 4><<<(unsigned)nt, RS_THREADS, 0, st>>>(ki, ko, vi, vo, n, 8 * p, bits, ss.hist + p * 256,
-                                                                  ss.counters + p, ss.status + (size_t)p * nt * 256);
+            WS_CUDA_CHECK(launch_pdl(rs_onesweep<K, 4>, dim3((unsigned)nt), dim3(RS_THREADS), 0, st, ki, ko, vi, vo, n,
+                                     8 * p, bits, ss.hist + p * 256, ss.counters + p, ss.status + (size_t)p * nt * 256));
         else
-            rs_onesweep<K, RS_ITEMS><<<(unsigned)nt, RS_THREADS, 0, st>>>(
-                ki, ko, vi, vo, n, 8 * p, bits, ss.hist + p * 256, ss.counters + p, ss.status + (size_t)p * nt * 256);
+            WS_CUDA_CHECK(launch_pdl(rs_onesweep<K, RS_ITEMS>, dim3((unsigned)nt), dim3(RS_THREADS), 0, st, ki, ko, vi, vo,
+                                     n, 8 * p, bits, ss.hist + p * 256, ss.counters + p,
+                                     ss.status + (size_t)p * nt * 256));
         WS_LAUNCH_CHECK(st, debug);
         K *tk = ki; ki = ko; ko = tk;
         uint32_t *tv = vi; vi = vo; vo = tv;

@@ -87,12 +87,12 @@ __global__ void __launch_bounds__(RF_THREADS, WS_RF_MINB) render_fwd(const __gri
     const float pixfx = (float)px;
     const f2 npy = pk2(-(float)py0, -(float)py1);
 
+    sm.init(lane);
+    pdl_wait();   // everything above is this CTA's own business; the tile ranges and the sorted list come from upstream
     const uint2 range = p.ranges[slot];
     const int n = (int)(range.y - range.x);
     const int nb = (n + ST_SEG - 1) / ST_SEG;
     const uint32_t *__restrict__ vals = p.vals + range.x;
-
-    sm.init(lane);
 
     int obj0 = 0, obj1 = 0;
     if (FLASH) {
@@ -284,9 +284,9 @@ int launch_render_fwd(const ws_view *v, int P, GeomState &gs, const uint32_t *va
     const unsigned grid = (unsigned)p.tiles_x * (unsigned)((p.H + WS_BLOCK_Y - 1) / WS_BLOCK_Y);
     p.jobs = nullptr; p.tiles_total = 0; p.job_alpha = nullptr; p.job_depth = nullptr;
     if (fl)
-        render_fwd<1><<<grid, RF_THREADS, 0, st>>>(tm, p);
+        WS_CUDA_CHECK(launch_pdl(render_fwd<1>, dim3(grid), dim3(RF_THREADS), 0, st, tm, p));
     else
-        render_fwd<0><<<grid, RF_THREADS, 0, st>>>(tm, p);
+        WS_CUDA_CHECK(launch_pdl(render_fwd<0>, dim3(grid), dim3(RF_THREADS), 0, st, tm, p));
     WS_LAUNCH_CHECK(st, v->debug);
     return WS_OK;
 }
