@@ -148,17 +148,21 @@ __device__ __forceinline__ void rs_tile_body(const K *__restrict__ kin, const ui
     }
 
     // ---- rank inside the warp, item by item (stable) ----
+    // The lanes holding equal digits find each other (match.any); their first lane adds the group's size to the
+    // warp's counter of that digit with a shared-memory atomic and hands the old value to the group.  The atomics of
+    // one warp on one address apply in program order (item order), and nothing else orders the items: the twelve
+    // match / atomic / shuffle chains overlap instead of running one after the other behind warp barriers.
 #pragma unroll
     for (int i = 0; i < ITEMS; i++) {
         const bool valid = FULL || (o0 + i * 32) < nt;
         const uint32_t d = valid ? ((uint32_t)(key[i] >> shift) & mask) : 0x100u;
         const uint32_t peers = __match_any_sync(0xffffffffu, d);
+        const int leader = __ffs(peers) - 1;
         uint32_t pre = 0;
-        if (valid) pre = s_whist[w][d];
-        __syncwarp();
-        if (valid && (peers & lt_mask) == 0) s_whist[w][d] = pre + __popc(peers);
-        __syncwarp();
+        if (valid && lane == leader) pre = atomicAdd(&s_whist[w][d], (uint32_t)__popc(peers));
+        pre = __shfl_sync(0xffffffffu, pre, leader);
         rank[i] = pre + __popc(peers & lt_mask);
+        __syncwarp(); // memory order between this item's atomics and the next item's (different lanes may lead)
     }
     __syncthreads();
 
