@@ -253,7 +253,8 @@ def stage_model(P, V, R, T, HW, M, npass, n_eval, n_contrib, Rf=None):
         "preprocess": P * (44 + 8 + 8) + V * (c + 65),
         "scan": 8 * ((P + 255) // 256),
         "emit_keys": 12 * P + 8 * ((P + 255) // 256) + 40 * V + 8 * R,
-        "sort": (4 * P + 4 * 16 * P) + (4 * R + npass * 16 * R),
+        # (the tile sort's digit histograms are counted by the emit pass: no read of the R keys for them)
+        "sort": (4 * P + 4 * 16 * P) + npass * 16 * R,
         # identify_ranges reads the sorted tile keys only; the blend kernels read the value list and gather the
         # 64-byte rows of the instances whose quadrant mask is not empty (Rf of them) from the per-Gaussian table
         "ranges_pack": 4 * R + 8 * T,
