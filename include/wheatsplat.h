@@ -281,6 +281,11 @@ int ws_allreduce_sum_f32(int32_t rank, int32_t world, int64_t numel, void *multi
 /* Tuning knobs of the multimem kernel (process-wide): independent 16-byte ld_reduce in flight per thread (2, 4 or 8;
  * default 4) and threads per CTA (default 512). */
 int ws_allreduce_tune(int32_t unroll, int32_t threads);
+/* With both a multicast address and peer pointers: the first `multicast_permille` thousandths of every rank's slice are
+ * reduced through the switch (multimem), the rest at the same time by `peer_ctas` extra CTAs with peer loads and
+ * stores (the in-switch reduction runs at about half the link rate; the peer path fills the links).  1000 = switch
+ * only (default).  Process-wide. */
+int ws_allreduce_split(int32_t multicast_permille, int32_t peer_ctas);
 
 /* Exchange + optimiser step of data-parallel training fused into ONE kernel (reduce-scatter, Adam, all-gather):
  * rank r owns the r-th slice of the flat parameter space [0, numel).  It reads the slice's gradient SUM over ranks

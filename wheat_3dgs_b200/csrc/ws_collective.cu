@@ -45,6 +45,9 @@ __global__ void __launch_bounds__(512) allreduce_multimem(float4 *mc, size_t beg
     for (; i < end4; i += stride) mc_st(mc + i, mc_ld_reduce(mc + i));
 }
 static int g_ar_unroll = 4, g_ar_threads = 512;
+// share (per mille) of a rank's slice that goes through the switch when both paths are available; the rest is
+// reduced by the SMs with peer loads and stores at the same time (ws_allreduce_split)
+static int g_ar_mc_permille = 1000, g_ar_peer_ctas = 148;
 
 constexpr int AR_MAX_WORLD = 16;
 struct PeerPtrs { float4 *p[AR_MAX_WORLD]; };
@@ -61,6 +64,37 @@ __global__ void __launch_bounds__(512) allreduce_peers(PeerPtrs peers, int world
     }
 }
 
+// Both paths in one launch.  The in-switch reduction runs at about half the link rate whatever the issuing grid
+// (0.57 ms for 248 MB at 8 GPUs, profiles/r02_exchange_sweep_8gpu.jsonl) and leaves link capacity idle; the peer
+// load/store path is bound by the links, not by the switch's reduction units.  CTAs [0, mc_ctas) reduce the first part
+// of the rank's slice through the switch, the other CTAs the rest with peer loads in rank order + peer stores.  Every
+// element still has exactly one reducer, so all ranks hold identical bits.
+__global__ void __launch_bounds__(512) allreduce_hybrid(float4 *mc, PeerPtrs peers, int world, size_t begin4, size_t mid4,
+                                                        size_t end4, int mc_ctas)
+{
+    if ((int)blockIdx.x < mc_ctas) {
+        const size_t stride = (size_t)mc_ctas * blockDim.x;
+        size_t i = begin4 + (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+        for (; i + 3 * stride < mid4; i += 4 * stride) {
+            float4 v[4];
+#pragma unroll
+            for (int k = 0; k < 4; k++) v[k] = mc_ld_reduce(mc + i + k * stride);
+#pragma unroll
+            for (int k = 0; k < 4; k++) mc_st(mc + i + k * stride, v[k]);
+        }
+        for (; i < mid4; i += stride) mc_st(mc + i, mc_ld_reduce(mc + i));
+    } else {
+        const size_t stride = (size_t)(gridDim.x - mc_ctas) * blockDim.x;
+        for (size_t i = mid4 + (size_t)(blockIdx.x - mc_ctas) * blockDim.x + threadIdx.x; i < end4; i += stride) {
+            float4 s = peers.p[0][i];
+            for (int k = 1; k < world; k++) {
+                const float4 v = peers.p[k][i];
+                s.x = __fadd_rn(s.x, v.x); s.y = __fadd_rn(s.y, v.y); s.z = __fadd_rn(s.z, v.z); s.w = __fadd_rn(s.w, v.w);
+            }
+            for (int k = 0; k < world; k++) peers.p[k][i] = s;
+        }
+    }
+}
 
 // ---- reduce-scatter + Adam + all-gather in ONE kernel (sharded optimiser step) ----
 // Parameters are replicated, so after the exchange every rank would run the same Adam step on the same summed
@@ -148,6 +182,16 @@ extern "C" int ws_allreduce_tune(int32_t unroll, int32_t threads)
     return WS_OK;
 }
 
+extern "C" int ws_allreduce_split(int32_t multicast_permille, int32_t peer_ctas)
+{
+    if (multicast_permille < 0 || multicast_permille > 1000 || peer_ctas < 1 || peer_ctas > 4096) {
+        set_error("ws_allreduce_split: share 0..1000 per mille, 1..4096 peer CTAs");
+        return WS_E_INVALID;
+    }
+    ws::g_ar_mc_permille = multicast_permille; ws::g_ar_peer_ctas = peer_ctas;
+    return WS_OK;
+}
+
 extern "C" int ws_allreduce_sum_f32(int32_t rank, int32_t world, int64_t numel, void *multicast_ptr,
                                     void *const *peer_ptrs, int32_t num_ctas, ws_stream_t stream)
 {
@@ -163,7 +207,16 @@ extern "C" int ws_allreduce_sum_f32(int32_t rank, int32_t world, int64_t numel, 
     if (begin4 == end4) return WS_OK;
     cudaStream_t st = (cudaStream_t)stream;
     const int ctas = num_ctas > 0 ? num_ctas : 148;
-    if (multicast_ptr) {
+    if (multicast_ptr && peer_ptrs && ws::g_ar_mc_permille < 1000) {
+        if (((uintptr_t)multicast_ptr & 15) != 0) { set_error("ws_allreduce_sum_f32: multicast pointer not 16-byte aligned"); return WS_E_INVALID; }
+        PeerPtrs pp;
+        for (int k = 0; k < world; k++) {
+            if (!peer_ptrs[k] || ((uintptr_t)peer_ptrs[k] & 15) != 0) { set_error("ws_allreduce_sum_f32: bad peer pointer %d", k); return WS_E_INVALID; }
+            pp.p[k] = (float4 *)peer_ptrs[k];
+        }
+        const size_t mid4 = begin4 + (end4 - begin4) * (size_t)ws::g_ar_mc_permille / 1000;
+        allreduce_hybrid<<<ctas + ws::g_ar_peer_ctas, 512, 0, st>>>((float4 *)multicast_ptr, pp, world, begin4, mid4, end4, ctas);
+    } else if (multicast_ptr) {
         if (((uintptr_t)multicast_ptr & 15) != 0) { set_error("ws_allreduce_sum_f32: multicast pointer not 16-byte aligned"); return WS_E_INVALID; }
         const int th = ws::g_ar_threads;
         if (ws::g_ar_unroll >= 8) allreduce_multimem<8><<<ctas, th, 0, st>>>((float4 *)multicast_ptr, begin4, end4);

@@ -116,10 +116,15 @@ __global__ void __launch_bounds__(RB_THREADS, WS_RB_MINB) render_bwd(const __gri
     // packed by pixel (for c . dL) ...
     const f2 dLr = pk2(dl0[0], dl1[0]), dLg = pk2(dl0[1], dl1[1]), dLb = pk2(dl0[2], dl1[2]),
              dLd = pk2(dl0[3], dl1[3]), dLa = pk2(dl0[4], dl1[4]);
-    // ... and by channel (for the colour / depth sums over the lane's two pixels).  Copied through opaque moves:
-    // ptxas would otherwise rebuild these pairs from the ones above with four moves per record.
-    const f2 rg0 = opaque2(pk2(dl0[0], dl0[1])), bd0 = opaque2(pk2(dl0[2], dl0[3])), rg1 = opaque2(pk2(dl1[0], dl1[1])),
-             bd1 = opaque2(pk2(dl1[2], dl1[3]));
+    // ... and by channel (for the colour / depth sums over the lane's two pixels), PERMUTED BY LANE so that the first two
+    // butterfly stages below need no selects: lanes with bit 4 set compute (b, depth) where the others compute (r, g)
+    // and vice versa -- every lane then keeps its pair "A" and sends its pair "B" -- and lanes with bit 3 set hold
+    // their pairs with the halves swapped -- every lane keeps the low half and sends the high one.  Copied through
+    // opaque moves: ptxas would otherwise rebuild these pairs from the ones above with moves per record.
+    const bool l16 = (lane & 16) != 0, l8 = (lane & 8) != 0;
+    const int ia = l16 ? 2 : 0, ib = l16 ? 0 : 2, lo_i = l8 ? 1 : 0, hi_i = l8 ? 0 : 1;
+    const f2 cA0 = opaque2(pk2(dl0[ia + lo_i], dl0[ia + hi_i])), cB0 = opaque2(pk2(dl0[ib + lo_i], dl0[ib + hi_i])),
+             cA1 = opaque2(pk2(dl1[ia + lo_i], dl1[ia + hi_i])), cB1 = opaque2(pk2(dl1[ib + lo_i], dl1[ib + hi_i]));
     const float bgr = __ldg(p.bg + 0), bgg = __ldg(p.bg + 1), bgb = __ldg(p.bg + 2);
     // -T_final * (bg . dL_dpixel): the background term of backward.cu:577-580 before its 1/(1-alpha)
     const f2 ntfbg = pk2(-Tf0 * (bgr * dl0[0] + bgg * dl0[1] + bgb * dl0[2]),
@@ -129,11 +134,13 @@ __global__ void __launch_bounds__(RB_THREADS, WS_RB_MINB) render_bwd(const __gri
         if (in0 && p.gt_mask) obj0 = __float2int_rz(p.gt_mask[pix0]);
         if (in1 && p.gt_mask) obj1 = __float2int_rz(p.gt_mask[pix1]);
     }
-    // where this lane's share of the reduced sums goes: after the butterflies lane l, l % 4 == 0, holds slot
-    // ((l>>4)&1)*4 + ((l>>3)&1)*2 + ((l>>2)&1) of the first eight sums and lanes 1 / 17 the last two
+    // where this lane's share of the reduced sums goes: after the butterflies lane l holds, of the first eight sums
+    // {r, g, b, depth, S g dx, S g dy, S g dx^2, S g dx dy}, the colour (bit 2 clear) or moment (bit 2 set) number
+    // 2 * bit 4 + bit 3, and of the last two {S g dy^2, S g} number bit 4; lanes 0 mod 4 write the former, lanes 1 and
+    // 17 the latter
     const bool low8 = (lane & 3) == 0;
     const bool writer = low8 || (lane & 15) == 1;
-    const int my_slot = low8 ? ((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1) : 8 + (lane >> 4);
+    const int my_slot = low8 ? ((lane >> 2) & 1) * 4 + ((lane >> 4) & 1) * 2 + ((lane >> 3) & 1) : 8 + (lane >> 4);
     const unsigned long long acc_lane = (unsigned long long)__cvta_generic_to_global(p.acc + my_slot);
     const ExpConsts ec = p.ec;
     // loop-carried state as scalar halves (packed at the point of use, see ws_render_fwd.cu):
@@ -207,51 +214,35 @@ __global__ void __launch_bounds__(RB_THREADS, WS_RB_MINB) render_bwd(const __gri
             Ta = k0 ? lo2(T) : Ta; Tb = k1 ? hi2(T) : Tb;
             Ra = lo2(Rn); Rb = hi2(Rn);
             // sums over the lane's two pixels
-            const f2 s_rg = fma2(bc2(hi2(wgt)), rg1, mul2(bc2(lo2(wgt)), rg0));
-            const f2 s_bd = fma2(bc2(hi2(wgt)), bd1, mul2(bc2(lo2(wgt)), bd0));
+            f2 sA = fma2(bc2(hi2(wgt)), cA1, mul2(bc2(lo2(wgt)), cA0));
+            const f2 sB = fma2(bc2(hi2(wgt)), cB1, mul2(bc2(lo2(wgt)), cB0));
             const f2 g = mul2(Gm, dopa);
             const f2 gy = mul2(g, dy), gyy = mul2(gy, dy);
             const float sg = lo2(g) + hi2(g), sgy = lo2(gy) + hi2(gy), sgyy = lo2(gyy) + hi2(gyy);
             const float sgx = sg * dx, sgxx = sgx * dx, sgxy = sgy * dx;
             float out;
             {
-                // transposing butterfly over 8 slots (lane l ends with slot l>>2 summed over the warp)
-                float v[8] = {lo2(s_rg), hi2(s_rg), lo2(s_bd), hi2(s_bd), sgx, sgy, sgxx, sgxy};
-                float e0 = sgyy, e1 = sg; // and over the last 2 slots
-                {
-                    const bool hi = (lane & 16) != 0;
-#pragma unroll
-                    for (int i = 0; i < 4; i++) {
-                        const float send = hi ? v[i] : v[i + 4];
-                        const float keep = hi ? v[i + 4] : v[i];
-                        v[i] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
-                    }
-                    const float send = hi ? e0 : e1;
-                    const float keep = hi ? e1 : e0;
-                    e0 = keep + __shfl_xor_sync(0xffffffffu, send, 16);
-                }
-                {
-                    const bool hi = (lane & 8) != 0;
-#pragma unroll
-                    for (int i = 0; i < 2; i++) {
-                        const float send = hi ? v[i] : v[i + 2];
-                        const float keep = hi ? v[i + 2] : v[i];
-                        v[i] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
-                    }
-                    e0 += __shfl_xor_sync(0xffffffffu, e0, 8);
-                }
-                {
-                    const bool hi = (lane & 4) != 0;
-                    const float send = hi ? v[0] : v[1];
-                    const float keep = hi ? v[1] : v[0];
-                    v[0] = keep + __shfl_xor_sync(0xffffffffu, send, 4);
-                    e0 += __shfl_xor_sync(0xffffffffu, e0, 4);
-                }
-                v[0] += __shfl_xor_sync(0xffffffffu, v[0], 2);
+                // Transposing butterflies.  Colour / depth sums: two select-free stages (the lane-permuted constants
+                // above put the pair to keep in sA and the pair to send in sB, then the half to keep low).
+                sA = add2(sA, pk2(__shfl_xor_sync(0xffffffffu, lo2(sB), 16), __shfl_xor_sync(0xffffffffu, hi2(sB), 16)));
+                const float col = lo2(sA) + __shfl_xor_sync(0xffffffffu, hi2(sA), 8);
+                // moments {S g dx, S g dy, S g dx^2, S g dx dy}: bit 4 picks the pair, bit 3 the member
+                const float mk0 = l16 ? sgxx : sgx, mk1 = l16 ? sgxy : sgy, ms0 = l16 ? sgx : sgxx, ms1 = l16 ? sgy : sgxy;
+                const float m0 = mk0 + __shfl_xor_sync(0xffffffffu, ms0, 16);
+                const float m1 = mk1 + __shfl_xor_sync(0xffffffffu, ms1, 16);
+                const float mom = (l8 ? m1 : m0) + __shfl_xor_sync(0xffffffffu, l8 ? m0 : m1, 8);
+                // the last two {S g dy^2, S g}: bit 4 picks
+                float e0 = (l16 ? sg : sgyy) + __shfl_xor_sync(0xffffffffu, l16 ? sgyy : sg, 16);
+                e0 += __shfl_xor_sync(0xffffffffu, e0, 8);
+                // bit 2: colour or moment
+                const bool l4 = (lane & 4) != 0;
+                float v0 = (l4 ? mom : col) + __shfl_xor_sync(0xffffffffu, l4 ? col : mom, 4);
+                e0 += __shfl_xor_sync(0xffffffffu, e0, 4);
+                v0 += __shfl_xor_sync(0xffffffffu, v0, 2);
                 e0 += __shfl_xor_sync(0xffffffffu, e0, 2);
-                v[0] += __shfl_xor_sync(0xffffffffu, v[0], 1);
+                v0 += __shfl_xor_sync(0xffffffffu, v0, 1);
                 e0 += __shfl_xor_sync(0xffffffffu, e0, 1);
-                out = low8 ? v[0] : e0;
+                out = low8 ? v0 : e0;
             }
             if (writer)
                 asm volatile("red.global.add.f32 [%0], %1;" ::"l"(acc_lane + (unsigned long long)gid * 48ull), "f"(out) : "memory");

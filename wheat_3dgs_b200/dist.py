@@ -23,6 +23,7 @@ import torch
 import torch.distributed as dist
 
 TRAIN_GRAD_FLOATS = lambda M: 3 + 3 + 3 * M + 1 + 3 + 4  # noqa: E731  per Gaussian
+DEFAULT_SPLIT = ""   # "permille,peer_ctas" for the hybrid all-reduce (multimem + peer path in one launch); "" = switch only
 
 
 def init_from_env(backend=None):
@@ -125,6 +126,12 @@ class SymmetricBucket:
             self.multicast = 0
         self.peers = (C.c_void_p * self.world)(*[int(p) for p in self.hdl.buffer_ptrs])
         self.num_ctas = int(os.environ.get("WS_ALLREDUCE_CTAS", "0"))
+        # share of every slice that goes through the switch, the rest by peer loads / stores at the same time
+        # (ws_allreduce_split; "permille,peer_ctas")
+        split = os.environ.get("WS_ALLREDUCE_SPLIT", DEFAULT_SPLIT)
+        if self.multicast and split:
+            pm, pc = (int(x) for x in split.split(","))
+            _lib.check(_lib.load().ws_allreduce_split(pm, pc), "ws_allreduce_split")
 
     def all_reduce_(self, numel=None):
         """SUM over ranks of tensor[:numel] (default: all of it), in place, on the current stream."""

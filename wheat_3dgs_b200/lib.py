@@ -18,7 +18,7 @@ SYMBOLS = [
     "ws_forward_prepare", "ws_forward_render", "ws_backward", "ws_mark_visible", "ws_knn_bytes",
     "ws_knn_dist2", "ws_multi_instance_opt", "ws_sort_bytes", "ws_sort_pairs_u64", "ws_sort_pairs_u32", "ws_set_binning_mode",
     "ws_loss_bytes", "ws_l1_ssim_forward", "ws_l1_ssim_backward", "ws_debug_fetch",
-    "ws_adam_step", "ws_densify_stats", "ws_allreduce_sum_f32", "ws_allreduce_tune",
+    "ws_adam_step", "ws_densify_stats", "ws_allreduce_sum_f32", "ws_allreduce_tune", "ws_allreduce_split",
     "ws_sharded_adam_step", "ws_densify_plan_bytes", "ws_densify_plan", "ws_densify_gather", "ws_reset_opacity",
     "ws_objeval_bytes", "ws_objeval_prepare", "ws_objeval_bin", "ws_objeval_render",
     "ws_launch_count", "ws_prof_enable", "ws_prof_read", "ws_prof_stage_name", "ws_debug_count_pairs",
@@ -144,6 +144,8 @@ def load():
     lib.ws_allreduce_sum_f32.argtypes = [i32, i32, i64, vp, C.POINTER(vp), i32, vp]
     lib.ws_allreduce_tune.restype = C.c_int
     lib.ws_allreduce_tune.argtypes = [i32, i32]
+    lib.ws_allreduce_split.restype = C.c_int
+    lib.ws_allreduce_split.argtypes = [i32, i32]
     lib.ws_adam_step.restype = C.c_int
     lib.ws_adam_step.argtypes = [i32, C.POINTER(WsAdamGroup), C.c_double, C.c_double, C.c_double, vp]
     lib.ws_densify_stats.restype = C.c_int
