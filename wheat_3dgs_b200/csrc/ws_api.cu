@@ -324,7 +324,7 @@ extern "C" int ws_forward_render(const ws_view *view, const ws_gaussians *g, con
         // the emit pass counts the tile keys' digits while it writes them: the sort needs no pass of its own for that
         const int end_bit = (int)get_higher_msb((uint32_t)T);
         // (the stage's first kernel also clears the sort's scratch words and the tile ranges)
-        { ProfScope ps(2, st); rc = launch_emit_tiles_ordered(g->P, W, H, radii, gs, bs.tkeys_a, bs.vals_a, st, debug, bs.sort.hist, (end_bit + 7) / 8,
+        { ProfScope ps(2, st); rc = launch_emit_tiles_ordered(g->P, W, H, radii, gs, bs.tkeys_a, bs.vals_a, st, debug, bs.sort.hist, (end_bit + 7) / 8, sort_digit_bits(end_bit),
                                                               bs.sort.hist, sort_scratch_words(R, end_bit), (uint32_t *)is.ranges, (size_t)T * 2); }
         ranges_cleared = true;
         if (rc != WS_OK) return rc;

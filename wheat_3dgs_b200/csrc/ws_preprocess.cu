@@ -545,7 +545,7 @@ __global__ void __launch_bounds__(WS_PRE_THREADS) emit_tiles_ordered(int P, int 
                                                                      const uint32_t *__restrict__ block_offsets,
                                                                      uint32_t *__restrict__ tkeys,
                                                                      uint32_t *__restrict__ vals,
-                                                                     uint32_t *__restrict__ hist, int npass)
+                                                                     uint32_t *__restrict__ hist, int npass, int wbits)
 {
     __shared__ uint32_t s_w[WS_PRE_THREADS / 32];
     // digit counts of the keys this CTA emits, all passes of the tile sort (pass p = key bits [8p, 8p+8)): the sort
@@ -612,16 +612,17 @@ __global__ void __launch_bounds__(WS_PRE_THREADS) emit_tiles_ordered(int P, int 
         if (hist) {
             // pass 0: neighbouring lanes hold neighbouring tiles, different bins.  Higher passes: runs of equal
             // digits (a Gaussian's row of tiles), one add per run by its first lane.
-            if (k < warp_total) atomicAdd(&s_hist[key & 255u], 1u);
+            const uint32_t dmask = (1u << wbits) - 1u;
+            if (k < warp_total) atomicAdd(&s_hist[key & dmask], 1u);
             for (int p = 1; p < npass; p++) {
-                const uint32_t d = key >> (8 * p);   // 0xffffff.. for idle lanes: never equal to a live digit
+                const uint32_t d = key >> (wbits * p);   // 0xffffff.. for idle lanes: never equal to a live digit
                 const uint32_t up = __shfl_up_sync(0xffffffffu, d, 1);
                 const bool head = lane == 0 || d != up;
                 const uint32_t heads = __ballot_sync(0xffffffffu, head);
                 if (head && k < warp_total) {
                     const uint32_t after = heads & ~((2u << lane) - 1u); // heads strictly above this lane
                     const uint32_t next = after ? (uint32_t)__ffs(after) - 1u : 32u;
-                    atomicAdd(&s_hist[p * 256 + (d & 255u)], next - (uint32_t)lane);
+                    atomicAdd(&s_hist[p * 256 + (d & dmask)], next - (uint32_t)lane);
                 }
             }
         }
@@ -636,7 +637,7 @@ __global__ void __launch_bounds__(WS_PRE_THREADS) emit_tiles_ordered(int P, int 
 }
 
 int launch_emit_tiles_ordered(int P, int W, int H, const int32_t *radii, GeomState &gs, uint32_t *tkeys,
-                              uint32_t *vals, cudaStream_t st, bool debug, uint32_t *hist, int npass,
+                              uint32_t *vals, cudaStream_t st, bool debug, uint32_t *hist, int npass, int wbits,
                               uint32_t *zero_a, size_t zero_a_words, uint32_t *zero_b, size_t zero_b_words)
 {
     if (npass > 4) hist = nullptr; // (more than 2^32 tiles: not reachable; the sort then counts for itself)
@@ -650,7 +651,7 @@ int launch_emit_tiles_ordered(int P, int W, int H, const int32_t *radii, GeomSta
                              gs.total + 1));
     WS_LAUNCH_CHECK(st, debug);
     WS_CUDA_CHECK(launch_pdl(emit_tiles_ordered, dim3(nb), dim3(WS_PRE_THREADS), 0, st, P, gx, gy, order, radii, gs.grec,
-                             gs.tiles_touched, gs.block_offsets, tkeys, vals, hist, npass));
+                             gs.tiles_touched, gs.block_offsets, tkeys, vals, hist, npass, wbits));
     WS_LAUNCH_CHECK(st, debug);
     return WS_OK;
 }

@@ -3,7 +3,7 @@
 // KNN simple_knn.cu:211-214).  No CUB, no Thrust.
 //
 //   rs_histogram   one read of the keys -> global digit histograms of every pass at once
-//   rs_scan_hist   exclusive scan of each pass's 256 bins -> digit base offsets
+//                  (the exclusive scan of a pass's 256 bins -> digit bases is redone by every CTA of the pass)
 //   rs_onesweep    one launch per 8-bit pass: every CTA takes a tile of 256 x 12 keys (ticket
 //                  from an atomic counter so predecessors are always resident), ranks them in
 //                  shared memory, learns the number of equal digits in all earlier tiles by a
@@ -69,8 +69,8 @@ __global__ void __launch_bounds__(256) rs_histogram(const K *__restrict__ keys, 
     for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
         const K key = keys[i];
         for (int p = 0; p < npass; p++) {
-            const int bits = min(8, end_bit - 8 * p);
-            const uint32_t d = (uint32_t)(key >> (8 * p)) & ((1u << bits) - 1u);
+            const int w = sort_digit_bits(end_bit), bits = min(w, end_bit - w * p);
+            const uint32_t d = (uint32_t)(key >> (w * p)) & ((1u << bits) - 1u);
             atomicAdd(&sh[p * 256 + d], 1u);
         }
     }
@@ -99,16 +99,6 @@ __device__ __forceinline__ uint32_t block_excl_scan_256(uint32_t v, uint32_t *s_
         if (k < w) base += s_w[k];
     __syncthreads();
     return base + inc - v;
-}
-
-__global__ void __launch_bounds__(256) rs_scan_hist(uint32_t *__restrict__ hist)
-{
-    __shared__ uint32_t s_w[RS_WARPS];
-    pdl_wait();
-    pdl_trigger();
-    uint32_t *h = hist + blockIdx.x * 256;
-    const uint32_t v = h[threadIdx.x];
-    h[threadIdx.x] = block_excl_scan_256(v, s_w);
 }
 
 __device__ __forceinline__ uint32_t ld_relaxed(const uint32_t *p)
@@ -205,8 +195,11 @@ __device__ __forceinline__ void rs_tile_body(const K *__restrict__ kin, const ui
         st_relaxed(my_status, ((excl + run) & RS_VAL_MASK) | RS_FLAG_INC);
     }
     const uint32_t dstart = block_excl_scan_256(run, s_w); // contains __syncthreads
+    // digit base = exclusive prefix of the pass's global histogram, scanned here by every CTA (256 values, one block
+    // scan) rather than by a kernel of its own between the histogram and the first pass
+    const uint32_t base = block_excl_scan_256(bins[tid], s_w);
     s_dstart[tid] = dstart;
-    s_goff[tid] = bins[tid] + excl - dstart;
+    s_goff[tid] = base + excl - dstart;
     __syncthreads();
 
     // ---- scatter into shared memory in sorted order ----
@@ -313,18 +306,16 @@ static int sort_pairs_impl(size_t n, K *keys_in, K *keys_out, uint32_t *vals_in,
         rs_histogram<K><<<hb, 256, 0, st>>>(keys_in, n, end_bit, ss.hist);
         WS_LAUNCH_CHECK(st, debug);
     }
-    WS_CUDA_CHECK(launch_pdl(rs_scan_hist, dim3(npass), dim3(256), 0, st, ss.hist));
-    WS_LAUNCH_CHECK(st, debug);
     K *ki = keys_in, *ko = keys_out;
     uint32_t *vi = vals_in, *vo = vals_out;
     for (int p = 0; p < npass; p++) {
-        const int bits = end_bit - 8 * p < 8 ? end_bit - 8 * p : 8;
+        const int w = sort_digit_bits(end_bit), bits = end_bit - w * p < w ? end_bit - w * p : w;
         if (sort_items(n) == 4)
             WS_CUDA_CHECK(launch_pdl(rs_onesweep<K, 4>, dim3((unsigned)nt), dim3(RS_THREADS), 0, st, ki, ko, vi, vo, n,
-                                     8 * p, bits, ss.hist + p * 256, ss.counters + p, ss.status + (size_t)p * nt * 256));
+                                     w * p, bits, ss.hist + p * 256, ss.counters + p, ss.status + (size_t)p * nt * 256));
         else
             WS_CUDA_CHECK(launch_pdl(rs_onesweep<K, RS_ITEMS>, dim3((unsigned)nt), dim3(RS_THREADS), 0, st, ki, ko, vi, vo,
-                                     n, 8 * p, bits, ss.hist + p * 256, ss.counters + p,
+                                     n, w * p, bits, ss.hist + p * 256, ss.counters + p,
                                      ss.status + (size_t)p * nt * 256));
         WS_LAUNCH_CHECK(st, debug);
         K *tk = ki; ki = ko; ko = tk;
