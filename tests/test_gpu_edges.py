@@ -34,7 +34,7 @@ def test_radix_sort_bit_exact_and_stable(n, bits):
     assert_exact("vals", G.n(vo).view(np.uint32), rv)
 
 
-@pytest.mark.parametrize("n,bits", [(0, 14), (1, 32), (31, 14), (3072, 32), (3073, 15), (100000, 14), (777, 1),
+@pytest.mark.parametrize("n,bits", [(0, 14), (1, 32), (31, 14), (3072, 32), (3073, 15), (4096, 14), (4097, 21), (100000, 14), (777, 1),
                                     (1 << 20, 32), (5000001, 14), (12345, 6)])
 def test_radix_sort_u32_bit_exact_and_stable(n, bits):
     # the form depth-first binning uses: Gaussians by 32 depth bits, instances by tile id

@@ -20,6 +20,6 @@ for spec in args:
     r = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "stage_times.py"), "12"], env=env,
                        capture_output=True, text=True)
     rows = dict(l.split()[:2] for l in r.stdout.splitlines() if l.strip())
-    print("%-28s fwd %s bwd %s pre_bwd %s sum %s %s" % (name, rows.get("render_fwd"), rows.get("render_bwd"),
-                                                        rows.get("preprocess_bwd"), rows.get("sum"),
+    print("%-28s fwd %s bwd %s pre_bwd %s pre %s emit %s sort %s sum %s %s" % (name, rows.get("render_fwd"), rows.get("render_bwd"),
+                                                        rows.get("preprocess_bwd"), rows.get("preprocess"), rows.get("emit_keys"), rows.get("sort"), rows.get("sum"),
                                                         r.stderr[-300:] if r.returncode else ""))

@@ -21,6 +21,12 @@
 
 namespace ws {
 
+#ifndef WS_PB_THREADS
+#define WS_PB_THREADS 128
+#endif
+constexpr int PB_THREADS = WS_PB_THREADS; // Gaussians (threads) per CTA; the SH block of a CTA is PB_THREADS x 12 M bytes of shared
+// memory.  128: the load / compute / store phases of twice as many resident CTAs overlap (0.148 -> 0.142 ms at config 2; 64: no gain)
+
 #define SH_C0 0.28209479177387814f
 #define SH_C1 0.4886025119029199f
 __constant__ float b_SH_C2[5] = {1.0925484305920792f, -1.0925484305920792f, 0.31539156525252005f,
@@ -107,21 +113,21 @@ __device__ __forceinline__ void cov3d_backward(const float *s, const float *q, c
 // A/B knob -DWS_PB_MINCTAS=4 (64 registers, 120 B of spills, 4 CTAs/SM instead of 3): 12 us faster on the raw-parameter
 // path, 6 us slower on the standard one -> left off.
 #ifdef WS_PB_MINCTAS
-#define WS_PB_BOUNDS __launch_bounds__(WS_PRE_THREADS, WS_PB_MINCTAS)
+#define WS_PB_BOUNDS __launch_bounds__(PB_THREADS, WS_PB_MINCTAS)
 #else
-#define WS_PB_BOUNDS __launch_bounds__(WS_PRE_THREADS)
+#define WS_PB_BOUNDS __launch_bounds__(PB_THREADS)
 #endif
 __global__ void WS_PB_BOUNDS preprocess_bwd(const PreBwdParams p)
 {
     extern __shared__ float4 s_sh4[];
     __shared__ float s_view[16], s_proj[16];
     const int tid = threadIdx.x;
-    const int base = blockIdx.x * WS_PRE_THREADS;
+    const int base = blockIdx.x * PB_THREADS;
     const int idx = base + tid;
     if (tid < 16) s_view[tid] = p.view[tid];
     else if (tid < 32) s_proj[tid - 16] = p.proj[tid - 16];
 
-    const int nvalid = min(WS_PRE_THREADS, p.P - base);
+    const int nvalid = min(PB_THREADS, p.P - base);
     const bool use_sh = (p.shs != nullptr && p.M > 0);
     const int row_f = 3 * p.M;
     const int srow = p.sh_vec4 ? (row_f / 4 + 1) * 4 : (row_f | 1); // row stride in floats
@@ -131,27 +137,27 @@ __global__ void WS_PB_BOUNDS preprocess_bwd(const PreBwdParams p)
             const int row4 = row_f / 4, srow4 = row4 + 1;
             const float4 *src = reinterpret_cast<const float4 *>(p.shs) + (size_t)base * row4;
             const int n4 = nvalid * row4;
-            for (int i = tid; i < n4; i += WS_PRE_THREADS) {
+            for (int i = tid; i < n4; i += PB_THREADS) {
                 int g = i / row4, c = i - g * row4;
                 s_sh4[g * srow4 + c] = __ldg(src + i);
             }
         } else if (p.shs_rest) {
             const int rest_f = row_f - 3;
             const float *src = p.shs + (size_t)base * 3;
-            for (int i = tid; i < nvalid * 3; i += WS_PRE_THREADS) {
+            for (int i = tid; i < nvalid * 3; i += PB_THREADS) {
                 int g = i / 3, c = i - g * 3;
                 s_sh[g * srow + c] = __ldg(src + i);
             }
             src = p.shs_rest + (size_t)base * rest_f;
             const int n = nvalid * rest_f;
-            for (int i = tid; i < n; i += WS_PRE_THREADS) {
+            for (int i = tid; i < n; i += PB_THREADS) {
                 int g = i / rest_f, c = i - g * rest_f;
                 s_sh[g * srow + 3 + c] = __ldg(src + i);
             }
         } else {
             const float *src = p.shs + (size_t)base * row_f;
             const int n = nvalid * row_f;
-            for (int i = tid; i < n; i += WS_PRE_THREADS) {
+            for (int i = tid; i < n; i += PB_THREADS) {
                 int g = i / row_f, c = i - g * row_f;
                 s_sh[g * srow + c] = __ldg(src + i);
             }
@@ -389,27 +395,27 @@ __global__ void WS_PB_BOUNDS preprocess_bwd(const PreBwdParams p)
             const int row4 = row_f / 4, srow4 = row4 + 1;
             float4 *dst = reinterpret_cast<float4 *>(p.dL_dsh) + (size_t)base * row4;
             const int n4 = nvalid * row4;
-            for (int i = tid; i < n4; i += WS_PRE_THREADS) {
+            for (int i = tid; i < n4; i += PB_THREADS) {
                 int g = i / row4, c = i - g * row4;
                 dst[i] = s_sh4[g * srow4 + c];
             }
         } else if (p.shs_rest) {
             const int rest_f = row_f - 3;
             float *dst = p.dL_dsh + (size_t)base * 3;
-            for (int i = tid; i < nvalid * 3; i += WS_PRE_THREADS) {
+            for (int i = tid; i < nvalid * 3; i += PB_THREADS) {
                 int g = i / 3, c = i - g * 3;
                 dst[i] = s_sh[g * srow + c];
             }
             dst = p.dL_dsh_rest + (size_t)base * rest_f;
             const int n = nvalid * rest_f;
-            for (int i = tid; i < n; i += WS_PRE_THREADS) {
+            for (int i = tid; i < n; i += PB_THREADS) {
                 int g = i / rest_f, c = i - g * rest_f;
                 dst[i] = s_sh[g * srow + 3 + c];
             }
         } else {
             float *dst = p.dL_dsh + (size_t)base * row_f;
             const int n = nvalid * row_f;
-            for (int i = tid; i < n; i += WS_PRE_THREADS) {
+            for (int i = tid; i < n; i += PB_THREADS) {
                 int g = i / row_f, c = i - g * row_f;
                 dst[i] = s_sh[g * srow + c];
             }
@@ -444,15 +450,15 @@ int launch_preprocess_bwd(const ws_view *v, const ws_gaussians *g, const int32_t
                  (!gr->dL_dsh || ((uintptr_t)gr->dL_dsh % 16) == 0)) ? 1 : 0;
     size_t smem = 0;
     if (use_sh)
-        smem = p.sh_vec4 ? (size_t)WS_PRE_THREADS * (row_f / 4 + 1) * 16 : (size_t)WS_PRE_THREADS * (row_f | 1) * 4;
+        smem = p.sh_vec4 ? (size_t)PB_THREADS * (row_f / 4 + 1) * 16 : (size_t)PB_THREADS * (row_f | 1) * 4;
     if (smem > 200 * 1024) {
         set_error("preprocess backward: %d SH coefficients need %zu bytes of shared memory", g->M, smem);
         return WS_E_UNSUPPORTED;
     }
     if (smem > 48 * 1024)
         WS_CUDA_CHECK(cudaFuncSetAttribute(preprocess_bwd, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    const int nb = (g->P + WS_PRE_THREADS - 1) / WS_PRE_THREADS;
-    preprocess_bwd<<<nb, WS_PRE_THREADS, smem, st>>>(p);
+    const int nb = (g->P + PB_THREADS - 1) / PB_THREADS;
+    preprocess_bwd<<<nb, PB_THREADS, smem, st>>>(p);
     WS_LAUNCH_CHECK(st, v->debug);
     return WS_OK;
 }

@@ -4,7 +4,7 @@
 //
 //   rs_histogram   one read of the keys -> global digit histograms of every pass at once
 //                  (the exclusive scan of a pass's 256 bins -> digit bases is redone by every CTA of the pass)
-//   rs_onesweep    one launch per 8-bit pass: every CTA takes a tile of 256 x 12 keys (ticket
+//   rs_onesweep    one launch per pass: every CTA takes a tile of 256 x 16 keys (12 with 64-bit keys) (ticket
 //                  from an atomic counter so predecessors are always resident), ranks them in
 //                  shared memory, learns the number of equal digits in all earlier tiles by a
 //                  decoupled look-back over per-(tile,digit) status words, and scatters.
@@ -24,7 +24,13 @@ namespace ws {
 
 constexpr int RS_THREADS = 256;
 constexpr int RS_WARPS = RS_THREADS / 32;
-constexpr int RS_ITEMS = 12;
+#ifndef WS_RS_ITEMS
+#define WS_RS_ITEMS 16
+#endif
+#ifndef WS_RS_MINB
+#define WS_RS_MINB 3
+#endif
+constexpr int RS_ITEMS = WS_RS_ITEMS;
 constexpr int RS_TILE = RS_THREADS * RS_ITEMS; // 3072 pairs per CTA
 constexpr int RS_MAX_PASSES = 8;
 #ifndef WS_RS_LOOK
@@ -39,10 +45,13 @@ constexpr uint32_t RS_VAL_MASK = (1u << 30) - 1;
 // Pairs per thread.  (4 for small inputs -- more CTAs per SM for the 1 M-pair depth sort -- was
 // measured slower, 25 vs 20 us per pass: a single-wave pass is bound by the look-back chain, which
 // grows with the number of tiles.)
-static inline int sort_items(size_t n) { (void)n; return RS_ITEMS; }
+constexpr int RS_ITEMS64 = 12;           // 64-bit keys (keys64 binning mode): 48 KB of static shared memory at most
+constexpr int RS_ITEMS_MIN = RS_ITEMS < RS_ITEMS64 ? RS_ITEMS : RS_ITEMS64;
+template <typename K> constexpr int items_of() { return sizeof(K) == 8 ? RS_ITEMS64 : RS_ITEMS; }
+// tiles the scratch is sized for (the smaller tile of the two key widths)
 size_t sort_tiles(size_t n)
 {
-    const size_t t = (size_t)RS_THREADS * sort_items(n);
+    const size_t t = (size_t)RS_THREADS * RS_ITEMS_MIN;
     return (n + t - 1) / t;
 }
 
@@ -230,7 +239,7 @@ __device__ __forceinline__ void rs_tile_body(const K *__restrict__ kin, const ui
 }
 
 template <typename K, int ITEMS>
-__global__ void __launch_bounds__(RS_THREADS, sizeof(K) == 4 ? 4 : 3)
+__global__ void __launch_bounds__(RS_THREADS, sizeof(K) == 4 ? WS_RS_MINB : 3)
 rs_onesweep(const K *__restrict__ keys_in, K *__restrict__ keys_out,
             const uint32_t *__restrict__ vals_in, uint32_t *__restrict__ vals_out, size_t n, int shift,
             int bits, const uint32_t *__restrict__ bins, uint32_t *__restrict__ counter,
@@ -297,7 +306,8 @@ static int sort_pairs_impl(size_t n, K *keys_in, K *keys_out, uint32_t *vals_in,
         return WS_E_INVALID;
     }
     const int npass = (end_bit + 7) / 8;
-    const size_t nt = sort_tiles(n);
+    constexpr int ITEMS = items_of<K>();
+    const size_t nt = (n + (size_t)RS_THREADS * ITEMS - 1) / ((size_t)RS_THREADS * ITEMS);
     if (!have_hist) {
         int rc = sort_clear_scratch(n, end_bit, ss, st);
         if (rc != WS_OK) return rc;
@@ -310,13 +320,8 @@ static int sort_pairs_impl(size_t n, K *keys_in, K *keys_out, uint32_t *vals_in,
     uint32_t *vi = vals_in, *vo = vals_out;
     for (int p = 0; p < npass; p++) {
         const int w = sort_digit_bits(end_bit), bits = end_bit - w * p < w ? end_bit - w * p : w;
-        if (sort_items(n) == 4)
-            WS_CUDA_CHECK(launch_pdl(rs_onesweep<K, 4>, dim3((unsigned)nt), dim3(RS_THREADS), 0, st, ki, ko, vi, vo, n,
-                                     w * p, bits, ss.hist + p * 256, ss.counters + p, ss.status + (size_t)p * nt * 256));
-        else
-            WS_CUDA_CHECK(launch_pdl(rs_onesweep<K, RS_ITEMS>, dim3((unsigned)nt), dim3(RS_THREADS), 0, st, ki, ko, vi, vo,
-                                     n, w * p, bits, ss.hist + p * 256, ss.counters + p,
-                                     ss.status + (size_t)p * nt * 256));
+        WS_CUDA_CHECK(launch_pdl(rs_onesweep<K, ITEMS>, dim3((unsigned)nt), dim3(RS_THREADS), 0, st, ki, ko, vi, vo, n,
+                                 w * p, bits, ss.hist + p * 256, ss.counters + p, ss.status + (size_t)p * nt * 256));
         WS_LAUNCH_CHECK(st, debug);
         K *tk = ki; ki = ko; ko = tk;
         uint32_t *tv = vi; vi = vo; vo = tv;
