@@ -12,12 +12,12 @@
 //   ndc2Pix                ->  double: DFMA((v+1), S, -1) * 0.5, rounded to float
 // The SH -> RGB evaluation is in the tolerance tier and written plainly.
 //
-// Memory behaviour.  One thread per Gaussian, 256 per CTA.  The SH block of a CTA
-// (256 x 3M floats, contiguous in the [P,M,3] input) is brought in with fully coalesced
+// Memory behaviour.  One thread per Gaussian, WS_PRE_THREADS (128) per CTA.  The SH block of a CTA
+// (128 x 3M floats, contiguous in the [P,M,3] input) is brought in with fully coalesced
 // 16-byte loads into padded shared memory (row stride 3M/4+1 float4 -> conflict-free
 // LDS.128), instead of each thread striding through its own 192 bytes.  Outputs are three
 // SoA float4 arrays (coalesced 512 B per warp store).  The CTA also reduces tiles_touched so
-// the prefix sum only has to scan P/256 block sums.
+// the prefix sum only has to scan P/128 block sums.
 #include "ws_common.cuh"
 
 namespace ws {
@@ -505,7 +505,7 @@ int launch_depth_sort(int P, GeomState &gs, cudaStream_t st, bool debug)
 }
 const uint32_t *depth_order(const GeomState &gs) { return gs.dvals_a; }
 
-// tiles_touched summed over blocks of 256 Gaussians taken in depth order
+// tiles_touched summed over blocks of WS_PRE_THREADS Gaussians taken in depth order
 // Also clears up to two word arrays for the stages behind it (the tile sort's histograms / status words and the tile
 // ranges): two memset launches less between the host learning R and the blend kernel.
 __global__ void __launch_bounds__(WS_PRE_THREADS) ordered_block_sums(int P, const uint32_t *__restrict__ order,
