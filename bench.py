@@ -123,6 +123,24 @@ class ClockSampler:
                 "power_w_max": max(pw) if pw else None, "reasons": sorted(reasons), "samples": len(sm)}
 
 
+def issue_active(kernel):
+    """Issue-slot utilisation of `kernel` from the committed ncu --set full capture (profiles/r02_ncu_full_raw.csv):
+    an issue-bound kernel's honest ceiling is issue slots, not FFMA lanes.  A profile figure, not a measurement of
+    this run."""
+    import csv
+    try:
+        with open(os.path.join(ROOT, "profiles", "r02_ncu_full_raw.csv")) as f:
+            rows = list(csv.reader(f))
+        hdr = rows[0]
+        ki, ii = hdr.index("Kernel Name"), hdr.index("smsp__issue_active.avg.pct_of_peak_sustained_active")
+        for r in rows[2:]:
+            if kernel in r[ki]:
+                return {"pct": float(r[ii]), "source": "profiles/r02_ncu_full_raw.csv (ncu --set full, config 2 view 17)"}
+    except (OSError, ValueError, IndexError):
+        pass
+    return None
+
+
 def load_peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -1282,7 +1300,7 @@ def main():
                                    % (r["fma"]["ffma_tflops"], peaks["sm_max_mhz"], nominal),
                     "frac_of_nominal": stages[top]["tflops"] / nominal,
                     "frac_at_observed_clock": stages[top]["tflops"] / (148 * 128 * 2 * sm_mhz * 1e6 / 1e12),
-                    "hbm_gbs": stages[top]["gbs"], "hbm_frac": stages[top]["hbm_frac"]}
+                    "hbm_gbs": stages[top]["gbs"], "hbm_frac": stages[top]["hbm_frac"], "issue_active": issue_active(top)}
         else:
             roof = {"kernel": top, "bound": "hbm", "achieved": stages[top]["gbs"], "peak": peaks["hbm_gbs"], "unit": "GB/s",
                     "frac": stages[top]["hbm_frac"], "traffic": traffic, "traffic_source": traffic_src,
