@@ -709,13 +709,17 @@ def run_orbit(args, job, workload, steps, warmup, with_e2e=True):
             sig, samples = fwd_signature(fw, P, W, H)
             parity = compare_signature(gold, sig, samples, name=workload)
             del fw
-    keep = [None]
+    # frames are independent: they go on three streams in turn (orbit.StreamRing, as orbit.render_360 does), so the
+    # short binning kernels of one frame run under the blend kernel of another
+    ring = orbit.StreamRing(int(os.environ.get("WS_ORBIT_STREAMS", "3")), dev)
+    keep = [None] * ring.n
 
     def step(i):
-        keep[0] = orbit.render_frame(g, cd[frame_of(i)], bg, SH_DEGREE)
+        with ring.stream(i):
+            keep[i % ring.n] = orbit.render_frame(g, cd[frame_of(i)], bg, SH_DEGREE)
 
     n0 = ops.launch_count()
-    ms = job.timed(step, steps, warmup)
+    ms = job.timed(step, steps, warmup, before=ring.fork, after=ring.join)
     launches = ops.launch_count() - n0
     out = dict(P=P, W=W, H=H, nv=nv, ms_total=ms, launches=launches, parity=parity)
     if with_e2e:
@@ -729,12 +733,13 @@ def run_orbit(args, job, workload, steps, warmup, with_e2e=True):
 
         def e2e_step(i):
             f = frame_of(i)
-            sl = pre.take(i, False)
-            cam = dict(cams[f], viewmatrix=sl["cam"][0:16].view(4, 4), projmatrix=sl["cam"][16:32].view(4, 4),
-                       campos=sl["cam"][32:35])
-            color = orbit.render_frame(g, cam, bg, SH_DEGREE)[0]
-            pre.release(sl)
-            done.record()
+            with ring.stream(i):
+                sl = pre.take(i, False)
+                cam = dict(cams[f], viewmatrix=sl["cam"][0:16].view(4, 4), projmatrix=sl["cam"][16:32].view(4, 4),
+                           campos=sl["cam"][32:35])
+                color = orbit.render_frame(g, cam, bg, SH_DEGREE)[0]
+                pre.release(sl)
+                done.record()
             k = nsteps[0] & 1
             nsteps[0] += 1
             evs[k].synchronize()            # the host buffer's previous frame has landed (it was "encoded")
@@ -748,6 +753,7 @@ def run_orbit(args, job, workload, steps, warmup, with_e2e=True):
             for e_ in evs:
                 e_.synchronize()
             torch.cuda.current_stream().wait_stream(copy_stream)
+            ring.join()
 
         for e_ in evs:
             e_.record()
@@ -828,9 +834,22 @@ def run_votes(args, job, workload, steps, warmup):
     del out_v
 
     # ---- (i) vote pass: one step = one view per rank
+    # (views are independent and the votes are float atomics into one accumulator: the views go on three streams in
+    # turn, orbit.StreamRing, so one view's binning kernels run under another's blend)
+    from wheat_3dgs_b200 import orbit
+    ring = orbit.StreamRing(int(os.environ.get("WS_ORBIT_STREAMS", "3")), dev)
     view_of = lambda i: my_views[i % len(my_views)]
+
+    def vote_step(i):
+        with ring.stream(i):
+            vote_view(view_of(i))
+
+    def fresh():
+        counts.zero_()
+        ring.fork()
+
     n0 = ops.launch_count()
-    ms = job.timed(lambda i: vote_view(view_of(i)), steps, warmup, before=counts.zero_)
+    ms = job.timed(vote_step, steps, warmup, before=fresh, after=ring.join)
     launches = ops.launch_count() - n0
     # the exchange + label assignment that end the pass (once per pass, timed separately)
     job.barrier()
@@ -853,14 +872,15 @@ def run_votes(args, job, workload, steps, warmup):
 
     def e2e_step(i):
         v = view_of(i)
-        sl = pre.take(i, False)
-        cam = dict(cams[v], viewmatrix=sl["cam"][0:16].view(4, 4), projmatrix=sl["cam"][16:32].view(4, 4),
-                   campos=sl["cam"][32:35])
-        vote_view(v, mask=sl["gt"], cam=cam)   # num_rendered comes back to the host inside the call
-        pre.release(sl)
+        with ring.stream(i):
+            sl = pre.take(i, False)
+            cam = dict(cams[v], viewmatrix=sl["cam"][0:16].view(4, 4), projmatrix=sl["cam"][16:32].view(4, 4),
+                       campos=sl["cam"][32:35])
+            vote_view(v, mask=sl["gt"], cam=cam)   # num_rendered comes back to the host inside the call
+            pre.release(sl)
 
     pre.prefetch(0)
-    ms_e2e = job.timed(e2e_step, steps, warmup, before=counts.zero_)
+    ms_e2e = job.timed(e2e_step, steps, warmup, before=fresh, after=ring.join)
 
     # ---- (ii) run_3d_seg per-seed loop on a sample of seeds (this rank's share)
     seg = segment.HeadSegmenter(g, cd, masks, bg, SH_DEGREE, iou_threshold=0.6)
