@@ -129,5 +129,6 @@ def test_vote_accumulator_sums_views_on_the_device():
                                                rs.tanfovy, rs.image_height, rs.image_width, g["shs"], 3, rs.campos,
                                                False, num_obj, False)[9]
         total += single
+    acc.join()   # the views ran on the accumulator's own streams
     assert torch.allclose(acc.all_counts, total, rtol=1e-5, atol=1e-6)
     assert torch.equal(acc.labels(), segment.multi_instance_opt(acc.all_counts))

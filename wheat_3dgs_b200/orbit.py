@@ -83,9 +83,13 @@ class StreamRing:
         self.streams = [torch.cuda.Stream(device=device) for _ in range(self.n)] if self.n > 1 else []
 
     def stream(self, i):
+        """Context of frame i's stream.  The stream first waits for what the current stream has queued so far (the
+        frame's inputs -- camera, mask -- are usually produced there)."""
         if not self.streams:
             return torch.cuda.stream(torch.cuda.current_stream())
-        return torch.cuda.stream(self.streams[i % self.n])
+        st = self.streams[i % self.n]
+        st.wait_stream(torch.cuda.current_stream())
+        return torch.cuda.stream(st)
 
     def fork(self):
         cur = torch.cuda.current_stream()
@@ -131,4 +135,10 @@ def render_360(g, cams, bg, sh_degree, rank=0, world=1, object_sets=None, on_fra
             else:
                 out.append((idx, color, depth, alpha, pred))
     ring.join()
+    if ring.streams:   # the frames were allocated on the ring's streams and will be read on the current one
+        cur = torch.cuda.current_stream()
+        for fr in out:
+            for t_ in fr[1:]:
+                if t_ is not None:
+                    t_.record_stream(cur)
     return out

@@ -29,22 +29,36 @@ class VoteAccumulator:
     """all_counts of run_3d_seg.py:86-97 on the device.  `add_view` runs one flashsplat forward whose votes are
     accumulated straight into `all_counts` (no per-view zero fill, no .cpu() round trip)."""
 
-    def __init__(self, num_obj, P, device="cuda"):
+    def __init__(self, num_obj, P, device="cuda", streams=3):
+        """`streams` > 1: consecutive add_view calls go on that many CUDA streams in turn (orbit.StreamRing): views are
+        independent and the votes are float atomics into one accumulator, so one view's short binning kernels run
+        under another's blend kernel (config 3: 729 -> 800 views/s).  `labels()` joins the streams first; the tuple
+        add_view returns belongs to the view's stream."""
+        from .orbit import StreamRing
         self.num_obj = int(num_obj)
         self.all_counts = torch.zeros((self.num_obj + 1, int(P)), dtype=torch.float32, device=device)
+        self._ring, self._n = StreamRing(streams, device), 0
+        self._ring.fork()
 
     def add_view(self, gt_mask, raster_settings, means3D, opacities, shs=None, colors_precomp=None, scales=None,
                  rotations=None, cov3D_precomp=None, unique_label=None):
         rs = raster_settings
         e = torch.Tensor([])
         o = lambda t: e if t is None else t
-        return _ops.flash_rasterize_gaussians(
-            gt_mask, unique_label, rs.bg, means3D, o(colors_precomp), opacities, o(scales), o(rotations),
-            rs.scale_modifier, o(cov3D_precomp), rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy,
-            rs.image_height, rs.image_width, o(shs), rs.sh_degree, rs.campos, rs.prefiltered, self.num_obj, rs.debug,
-            used_count_out=self.all_counts)
+        with self._ring.stream(self._n):
+            self._n += 1
+            return _ops.flash_rasterize_gaussians(
+                gt_mask, unique_label, rs.bg, means3D, o(colors_precomp), opacities, o(scales), o(rotations),
+                rs.scale_modifier, o(cov3D_precomp), rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy,
+                rs.image_height, rs.image_width, o(shs), rs.sh_degree, rs.campos, rs.prefiltered, self.num_obj, rs.debug,
+                used_count_out=self.all_counts)
+
+    def join(self):
+        """The current stream waits for every view added so far (call before reading all_counts)."""
+        self._ring.join()
 
     def labels(self, gamma=0.0):
+        self.join()
         return multi_instance_opt(self.all_counts, gamma)
 
 
