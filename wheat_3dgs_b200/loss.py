@@ -69,6 +69,57 @@ def ssim_l1_sums(img, gt):
     return _SsimL1Sums.apply(img, gt)
 
 
+_WEIGHTS = {}
+
+
+def _loss_weights(planes, n, lam, device):
+    """[planes, 2] weights of the per-plane {SSIM sum, L1 sum} in the training loss (cached per shape / lambda)."""
+    key = (planes, n, float(lam), str(device))
+    w = _WEIGHTS.get(key)
+    if w is None:
+        w = torch.tensor([[-float(lam) / n, (1.0 - float(lam)) / n]] * planes, dtype=torch.float32, device=device)
+        _WEIGHTS[key] = w
+    return w
+
+
+class _L1SsimLoss(torch.autograd.Function):
+    """The whole loss of train_vanilla_3dgs.py:78-79 as ONE autograd node: the scalar is a dot product of the kernel's
+    per-plane sums with cached weights (two small launches), its backward one scale + the fused backward kernel.  Built
+    from torch ops on `ssim_l1_sums` the same value costs seventeen one-element kernels per iteration, forward and
+    backward (68 us of launch gaps in a 2.7 ms iteration)."""
+
+    @staticmethod
+    def forward(ctx, img, gt, lam):
+        L = _lib.load()
+        planes, H, W = _planes(img, gt)
+        x = img.detach().float().contiguous()
+        y = gt.detach().float().contiguous()
+        sums = torch.empty((planes, 2), dtype=torch.float32, device=x.device)
+        nbytes = L.ws_loss_bytes(planes, H, W)
+        scratch = torch.empty((nbytes,), dtype=torch.uint8, device=x.device)
+        with torch.cuda.device(x.device):
+            _lib.check(L.ws_l1_ssim_forward(planes, H, W, x.data_ptr(), y.data_ptr(), sums.data_ptr(),
+                                            scratch.data_ptr(), nbytes, _stream()), "ws_l1_ssim_forward")
+        w = _loss_weights(planes, planes * H * W, lam, x.device)
+        ctx.save_for_backward(x, y, scratch, w)
+        ctx.dims = (planes, H, W)
+        ctx.in_shape, ctx.in_dtype = img.shape, img.dtype
+        return torch.dot(sums.view(-1), w.view(-1)) + float(lam)
+
+    @staticmethod
+    def backward(ctx, g):
+        L = _lib.load()
+        x, y, scratch, w = ctx.saved_tensors
+        planes, H, W = ctx.dims
+        coef = (w * g.detach().float()).contiguous()   # [planes, 2] = {a, b} per plane
+        grad = torch.empty_like(x)
+        with torch.cuda.device(x.device):
+            _lib.check(L.ws_l1_ssim_backward(planes, H, W, x.data_ptr(), y.data_ptr(), coef.data_ptr(), 1,
+                                             scratch.data_ptr(), scratch.numel(), grad.data_ptr(), _stream()),
+                       "ws_l1_ssim_backward")
+        return grad.view(ctx.in_shape).to(ctx.in_dtype), None, None
+
+
 def l1_loss(network_output, gt):
     """utils/loss_utils.py:17-18."""
     planes, H, W = _planes(network_output, gt)
@@ -92,6 +143,4 @@ def ssim(img1, img2, window_size=11, size_average=True):
 def l1_ssim_loss(image, gt_image, lambda_dssim=0.2):
     """train_vanilla_3dgs.py:78-79: (1 - lambda) * l1_loss + lambda * (1 - ssim), one forward launch pair
     and one backward launch."""
-    planes, H, W = _planes(image, gt_image)
-    s = ssim_l1_sums(image, gt_image).sum(dim=0) / float(planes * H * W)
-    return (1.0 - lambda_dssim) * s[1] + lambda_dssim * (1.0 - s[0])
+    return _L1SsimLoss.apply(image, gt_image, float(lambda_dssim))
