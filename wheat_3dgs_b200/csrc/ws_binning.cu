@@ -99,6 +99,13 @@ int make_grec_tensor_map(TensorMap *tm, const GRec *grec, int P)
         }
         encode = (EncodeTiledFn)fn;
     }
+    // the descriptor depends on the table's address and row count only: the last one is kept per thread (the forward
+    // and the backward of a view, and every view of a trainer whose allocator hands back the same block, reuse it)
+    static thread_local struct { const GRec *grec; int P; TensorMap tm; bool ok; } last = {nullptr, 0, {}, false};
+    if (last.ok && last.grec == grec && last.P == P) {
+        *tm = last.tm;
+        return WS_OK;
+    }
     const cuuint64_t dims[2] = {16, (cuuint64_t)(P > 0 ? P : 1)};
     const cuuint64_t strides[1] = {sizeof(GRec)};
     const cuuint32_t box[2] = {16, 1};
@@ -110,6 +117,7 @@ int make_grec_tensor_map(TensorMap *tm, const GRec *grec, int P)
         set_error("cuTensorMapEncodeTiled failed (%d) for the %d x 64-byte Gaussian table at %p", (int)r, P, (const void *)grec);
         return WS_E_CUDA;
     }
+    last.grec = grec; last.P = P; last.tm = *tm; last.ok = true;
     return WS_OK;
 }
 
