@@ -125,8 +125,11 @@ size_t ws_binning_bytes(int64_t num_rendered, int32_t width, int32_t height);
 
 /* Forward, phase A: preprocessCUDA + prefix sum of tiles_touched
  * (rasterizer_impl.cu:248-282).  Writes radii[P] (int32, every element) and, if fl != NULL,
- * image_xys / gs_depth.  Synchronises `stream` once to read num_rendered (as the reference's
- * cudaMemcpy at :282 does).  Returns num_rendered >= 0. */
+ * image_xys / gs_depth.  Blocks the calling thread until the prefix sum has delivered num_rendered (the reference's
+ * cudaMemcpy at :282): the count arrives through a mailbox in mapped pinned memory written from a side stream, so
+ * `stream` itself is NOT drained -- the depth sort this call queued behind the prefix sum keeps running while the
+ * caller sizes the binning scratch.  Not capturable into a CUDA graph (neither is the reference's copy).
+ * Returns num_rendered >= 0. */
 int64_t ws_forward_prepare(const ws_view *view, const ws_gaussians *g, int32_t *radii, void *geom,
                            size_t geom_bytes, const ws_flash *fl, ws_stream_t stream);
 
