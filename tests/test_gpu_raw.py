@@ -64,15 +64,20 @@ def test_raw_entry_matches_getters_plus_rasterizer(name):
     sc, cam, lg, deg = cases.dgr_inputs(name)
     o = _both(sc, cam, deg, lg)
     a, b = o["raw"], o["getters"]
+    # both formulations end in the same blend backward, whose float atomics land in a different order every run:
+    # the tolerance floor is that run-to-run spread, measured here on two more runs of the getter formulation
+    # (un-normalised quaternions of norm 0.2 amplify it five-fold in the rotation gradient)
+    b2, b3 = _both(sc, cam, deg, lg)["getters"], _both(sc, cam, deg, lg)["getters"]
     # the in-kernel activations are the float operations torch's CUDA kernels perform: same radii, same pixels
     assert np.array_equal(a["radii"], b["radii"]), "%d radii differ" % (a["radii"] != b["radii"]).sum()
     for k in ("color", "depth", "alpha"):
         assert_image(k, a[k], b[k])
         assert np.array_equal(a[k].view(np.uint32), b[k].view(np.uint32)), k + " is not bit-identical"
-    assert_grad("means2D", a["m2d"], b["m2d"])
+    sp = lambda x, y, z: float(max(np.abs(x - y).max(), np.abs(x - z).max(), np.abs(y - z).max()))
+    assert_grad("means2D", a["m2d"], b["m2d"], spread=sp(b["m2d"], b2["m2d"], b3["m2d"]))
     for k in a["grads"]:
         assert a["grads"][k].shape == b["grads"][k].shape
-        assert_grad(k, a["grads"][k], b["grads"][k])
+        assert_grad(k, a["grads"][k], b["grads"][k], spread=sp(b["grads"][k], b2["grads"][k], b3["grads"][k]))
 
 
 def test_raw_entry_at_training_size_and_degenerate_quaternions():
@@ -86,11 +91,13 @@ def test_raw_entry_at_training_size_and_degenerate_quaternions():
     o = _both(sc, cam, 3, lg)
     a, b = o["raw"], o["getters"]
     b2 = _both(sc, cam, 3, lg)["getters"]   # the blend backward sums with float atomics: its own run-to-run spread
+    b3 = _both(sc, cam, 3, lg)["getters"]
     assert (a["radii"] != b["radii"]).sum() == 0
     for k in ("color", "depth", "alpha"):
         assert_image(k, a[k], b[k])
         assert np.array_equal(a[k].view(np.uint32), b[k].view(np.uint32)), k + " is not bit-identical"
     for k in a["grads"]:
         assert np.all(np.isfinite(a["grads"][k]))
-        spread = float(np.abs(b["grads"][k] - b2["grads"][k]).max())
+        spread = float(max(np.abs(b["grads"][k] - b2["grads"][k]).max(), np.abs(b["grads"][k] - b3["grads"][k]).max(),
+                           np.abs(b2["grads"][k] - b3["grads"][k]).max()))
         assert_grad(k, a["grads"][k], b["grads"][k], spread=spread)

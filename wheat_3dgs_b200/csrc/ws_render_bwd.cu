@@ -122,6 +122,14 @@ __global__ void __launch_bounds__(RB_THREADS, WS_RB_MINB) render_bwd(const __gri
     // their pairs with the halves swapped -- every lane keeps the low half and sends the high one.  Copied through
     // opaque moves: ptxas would otherwise rebuild these pairs from the ones above with moves per record.
     const bool l16 = (lane & 16) != 0, l8 = (lane & 8) != 0;
+    // the same lane bits as all-ones / zero words for bitwise selects in the butterflies: a predicated select needs its
+    // predicate, and with seven predicate registers ptxas rebuilt these from the thread id for every record (ten
+    // instructions); a LOP3 with the mask in a register needs nothing
+    // (passed through a self-shuffle: ptxas would otherwise recognise the masks as lane predicates and go back to
+    // predicated selects)
+    const uint32_t m16 = __shfl_sync(0xffffffffu, l16 ? 0xffffffffu : 0u, lane),
+                   m8 = __shfl_sync(0xffffffffu, l8 ? 0xffffffffu : 0u, lane),
+                   m4 = __shfl_sync(0xffffffffu, (lane & 4) ? 0xffffffffu : 0u, lane);
     const int ia = l16 ? 2 : 0, ib = l16 ? 0 : 2, lo_i = l8 ? 1 : 0, hi_i = l8 ? 0 : 1;
     const f2 cA0 = opaque2(pk2(dl0[ia + lo_i], dl0[ia + hi_i])), cB0 = opaque2(pk2(dl0[ib + lo_i], dl0[ib + hi_i])),
              cA1 = opaque2(pk2(dl1[ia + lo_i], dl1[ia + hi_i])), cB1 = opaque2(pk2(dl1[ib + lo_i], dl1[ib + hi_i]));
@@ -141,8 +149,21 @@ __global__ void __launch_bounds__(RB_THREADS, WS_RB_MINB) render_bwd(const __gri
     const bool low8 = (lane & 3) == 0;
     const bool writer = low8 || (lane & 15) == 1;
     const int my_slot = low8 ? ((lane >> 2) & 1) * 4 + ((lane >> 4) & 1) * 2 + ((lane >> 3) & 1) : 8 + (lane >> 4);
-    const unsigned long long acc_lane = (unsigned long long)__cvta_generic_to_global(p.acc + my_slot);
-    const ExpConsts ec = p.ec;
+    // (the lane's accumulator base through shuffles too: ptxas otherwise rebuilds it from the parameter for every record)
+    unsigned long long acc_lane = (unsigned long long)__cvta_generic_to_global(p.acc + my_slot);
+    {
+        const int nxt = (lane + 1) & 31;   // a round trip over two lanes: the value is the lane's own again
+        unsigned lo = (unsigned)acc_lane, hi = (unsigned)(acc_lane >> 32);
+        lo = __shfl_sync(0xffffffffu, __shfl_sync(0xffffffffu, lo, nxt), (lane + 31) & 31);
+        hi = __shfl_sync(0xffffffffu, __shfl_sync(0xffffffffu, hi, nxt), (lane + 31) & 31);
+        acc_lane = ((unsigned long long)hi << 32) | lo;
+    }
+    // (the exp constants through a self-shuffle as well: ptxas otherwise reloads them from the constant bank for
+    // every record, two LDC per record)
+    ExpConsts ec;
+    ec.a = __shfl_sync(0xffffffffu, lane == 0 ? p.ec.a : 0.0f, 0);
+    ec.m = __shfl_sync(0xffffffffu, lane == 0 ? p.ec.m : 0.0f, 0);
+    ec.one = __shfl_sync(0xffffffffu, lane == 0 ? p.ec.one : 0.0f, 0);
     // loop-carried state as scalar halves (packed at the point of use, see ws_render_fwd.cu):
     // T = transmittance in front of the current record, R = sum over the records behind it of
     // alpha_j T_j (c_j . dL_dC + depth_j dL_dD + dL_dA)
@@ -227,16 +248,16 @@ __global__ void __launch_bounds__(RB_THREADS, WS_RB_MINB) render_bwd(const __gri
                 sA = add2(sA, pk2(__shfl_xor_sync(0xffffffffu, lo2(sB), 16), __shfl_xor_sync(0xffffffffu, hi2(sB), 16)));
                 const float col = lo2(sA) + __shfl_xor_sync(0xffffffffu, hi2(sA), 8);
                 // moments {S g dx, S g dy, S g dx^2, S g dx dy}: bit 4 picks the pair, bit 3 the member
-                const float mk0 = l16 ? sgxx : sgx, mk1 = l16 ? sgxy : sgy, ms0 = l16 ? sgx : sgxx, ms1 = l16 ? sgy : sgxy;
+                const float mk0 = bsel(m16, sgxx, sgx), mk1 = bsel(m16, sgxy, sgy), ms0 = bsel(m16, sgx, sgxx),
+                            ms1 = bsel(m16, sgy, sgxy);
                 const float m0 = mk0 + __shfl_xor_sync(0xffffffffu, ms0, 16);
                 const float m1 = mk1 + __shfl_xor_sync(0xffffffffu, ms1, 16);
-                const float mom = (l8 ? m1 : m0) + __shfl_xor_sync(0xffffffffu, l8 ? m0 : m1, 8);
+                const float mom = bsel(m8, m1, m0) + __shfl_xor_sync(0xffffffffu, bsel(m8, m0, m1), 8);
                 // the last two {S g dy^2, S g}: bit 4 picks
-                float e0 = (l16 ? sg : sgyy) + __shfl_xor_sync(0xffffffffu, l16 ? sgyy : sg, 16);
+                float e0 = bsel(m16, sg, sgyy) + __shfl_xor_sync(0xffffffffu, bsel(m16, sgyy, sg), 16);
                 e0 += __shfl_xor_sync(0xffffffffu, e0, 8);
                 // bit 2: colour or moment
-                const bool l4 = (lane & 4) != 0;
-                float v0 = (l4 ? mom : col) + __shfl_xor_sync(0xffffffffu, l4 ? col : mom, 4);
+                float v0 = bsel(m4, mom, col) + __shfl_xor_sync(0xffffffffu, bsel(m4, col, mom), 4);
                 e0 += __shfl_xor_sync(0xffffffffu, e0, 4);
                 v0 += __shfl_xor_sync(0xffffffffu, v0, 2);
                 e0 += __shfl_xor_sync(0xffffffffu, e0, 2);
