@@ -243,9 +243,12 @@ def test_against_live_reference(cfg):
     torch.cuda.synchronize()
     r2 = {k: v.clone() for k, v in rr.backward(dc, dd, da).items()}
     torch.cuda.synchronize()
+    r3 = {k: v.clone() for k, v in rr.backward(dc, dd, da).items()}
+    torch.cuda.synchronize()
     mine = G.backward(gd, cd, bg, 3, fw, dc, dd, da)
     for k, m in zip(GRAD_NAMES, mine):
-        spread = float((r1[k] - r2[k]).abs().max())
+        # the reference's own run-to-run spread (its float atomics), the largest of three runs' pairwise differences
+        spread = float(max((r1[k] - r2[k]).abs().max(), (r1[k] - r3[k]).abs().max(), (r2[k] - r3[k]).abs().max()))
         assert_grad(k, G.n(m).reshape(-1), G.n(r1[k]).reshape(-1), spread=spread)
 
 
