@@ -158,6 +158,28 @@ size_t ws_knn_bytes(int32_t P);
 int ws_knn_dist2(int32_t P, const float *points, float *mean_dists, void *scratch, size_t scratch_bytes,
                  ws_stream_t stream);
 
+/* ws_knn_dist2 for callers that cannot provide scratch.  No counterpart in the reference (its distCUDA2 allocates
+ * through thrust, KNN/simple_knn.cu:195-217); this entry point exists because ws_knn_dist2 asks the caller for
+ * ws_knn_bytes(P) bytes of device memory and some callers have no means of getting them:
+ *   - a binding that only speaks this C ABI (ctypes / cgo / JNI without a CUDA runtime of its own) and is handed the
+ *     `points` and `mean_dists` pointers by another component: it can pass pointers on but has no cudaMalloc to call;
+ *   - a plug-in inside a process whose device memory is owned by one pool (torch's caching allocator configured to
+ *     take the whole card, a renderer with a fixed budget): a second allocator's cudaMalloc fails or fragments it;
+ *   - code on a path where allocating is forbidden because it synchronises the device (cudaMalloc / cudaFree do).
+ * The scratch is a fixed array inside the library image instead: 8 MiB of device memory on EVERY GPU that loads
+ * libwheatsplat.so, held until the process exits whether or not this function is ever called.  It serves at most
+ * WS_KNN_STATIC_MAX_POINTS points; a larger P returns WS_E_SCRATCH (ws_last_error says to use ws_knn_dist2) and
+ * launches nothing.  The function calls no cudaMalloc, cudaFree or other allocating routine.  Results are bit-identical
+ * to ws_knn_dist2 on the same input.
+ * First call on a device: looks up the array's device address (cudaGetSymbolAddress, with that device current) and
+ * remembers it per device ordinal; make this first call outside any stream capture.  Later calls only launch.
+ * Sharing: every call on a device uses the same array and finds the previous call's contents in it; the function
+ * clears the words that must start at zero itself, on `stream`.  Two calls whose kernels can overlap on the GPU (two
+ * streams, two host threads, two processes' worth of streams in one context) race on the array and give wrong
+ * distances: order them on one stream or with events.  The current device must be the one `points` lives on. */
+#define WS_KNN_STATIC_MAX_POINTS 300000
+int ws_knn_dist2_static(int32_t P, const float *points, float *mean_dists, ws_stream_t stream);
+
 /* multi_instance_opt (run_3d_seg.py:54-72): labels[i,j] = argmax over normalize([sum_j - A_ij, A_ij])
  * with gamma added to row 0.  all_contrib float[num_rows,P] -> labels uint8[num_rows,P]. */
 int ws_multi_instance_opt(int32_t num_rows, int32_t P, const float *all_contrib, float gamma,

@@ -6,6 +6,7 @@
 //   ws_multi_instance_opt  run_3d_seg.py:54-72 fused into one pass over the vote matrix (the
 //                          reference loops over labels in Python, a handful of torch kernels each).
 #include <float.h>
+#include <mutex>
 #include "ws_common.cuh"
 
 namespace ws {
@@ -296,6 +297,75 @@ extern "C" int ws_knn_dist2(int32_t P, const float *points, float *mean_dists, v
     if (rc != WS_OK) return rc;
     const int nb = (P + 1023) / 1024;
     knn_box_minmax<<<nb, 1024, 0, st>>>(P, points, vf, ks.boxes);
+    WS_LAUNCH_CHECK(st, false);
+    knn_box_mean_dist<<<(P + 255) / 256, 256, 0, st>>>(P, points, vf, ks.boxes, mean_dists);
+    WS_LAUNCH_CHECK(st, false);
+    return WS_OK;
+}
+
+// ---- ws_knn_dist2_static: distCUDA2 for callers that have no way to obtain device scratch -------------------------
+// The scratch of the search (Morton keys and point indices in two copies, the per-1024-point boxes, the radix sort's
+// histograms and look-back words) lives in the array below instead of in caller memory.  The array is part of the
+// library image: every GPU that loads libwheatsplat.so sets these 8 MiB aside until the process exits, used or not.
+// In host code `g_knn_static` is only a handle for the runtime (its host-side value is not a device address and must
+// never reach a kernel); the device address is asked for once per device with cudaGetSymbolAddress.
+constexpr size_t KNN_STATIC_BYTES = (size_t)8 << 20;
+static __device__ __align__(256) unsigned char g_knn_static[KNN_STATIC_BYTES];
+constexpr int KNN_STATIC_MAX_DEVICES = 64;
+static void *g_knn_static_ptr[KNN_STATIC_MAX_DEVICES] = {};
+static std::mutex g_knn_static_mu;
+
+// device address of g_knn_static on the CURRENT device (looked up on the first call per device, remembered after)
+static int knn_static_base(char **base)
+{
+    int dev = -1;
+    WS_CUDA_CHECK(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= KNN_STATIC_MAX_DEVICES) {
+        set_error("ws_knn_dist2_static: device ordinal %d not supported (at most %d devices)", dev, KNN_STATIC_MAX_DEVICES);
+        return WS_E_UNSUPPORTED;
+    }
+    std::lock_guard<std::mutex> lock(g_knn_static_mu);
+    if (!g_knn_static_ptr[dev]) {
+        void *ptr = nullptr;
+        WS_CUDA_CHECK(cudaGetSymbolAddress((void **)&ptr, g_knn_static));
+        if (!ptr) { set_error("ws_knn_dist2_static: cudaGetSymbolAddress returned a null address"); return WS_E_CUDA; }
+        g_knn_static_ptr[dev] = ptr;
+    }
+    *base = (char *)g_knn_static_ptr[dev];
+    return WS_OK;
+}
+
+extern "C" int ws_knn_dist2_static(int32_t P, const float *points, float *mean_dists, ws_stream_t stream)
+{
+    if (P < 0 || (P > 0 && (!points || !mean_dists))) { set_error("ws_knn_dist2_static: bad arguments"); return WS_E_INVALID; }
+    if (P == 0) return WS_OK;
+    if (P > WS_KNN_STATIC_MAX_POINTS || ws_knn_bytes(P) > KNN_STATIC_BYTES) {
+        set_error("ws_knn_dist2_static: %d points exceed the built-in scratch (limit %d points, %zu bytes); "
+                  "call ws_knn_dist2 with ws_knn_bytes(P) bytes of your own scratch instead",
+                  P, WS_KNN_STATIC_MAX_POINTS, KNN_STATIC_BYTES);
+        return WS_E_SCRATCH;
+    }
+    char *base = nullptr;
+    int rc = knn_static_base(&base);
+    if (rc != WS_OK) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    // Same carve and same launches as ws_knn_dist2.  What the previous call left in the array does not matter: the
+    // bbox partials, keys, indices and boxes are all written before they are read, and the only words that must start
+    // at zero (the sort's histograms, tile tickets and look-back status) are cleared on `st` by the sort itself.
+    KnnScratch ks = KnnScratch::from(base, (size_t)P, nullptr);
+    int nblk = (P + 256 * 8 - 1) / (256 * 8);
+    if (nblk > 1024) nblk = 1024;
+    knn_bbox_partial<<<nblk, 256, 0, st>>>(P, points, ks.part);
+    WS_LAUNCH_CHECK(st, false);
+    knn_bbox_final<<<1, 32, 0, st>>>(nblk, ks.part, ks.mm);
+    WS_LAUNCH_CHECK(st, false);
+    knn_morton<<<(P + 255) / 256, 256, 0, st>>>(P, points, ks.mm, ks.keys_a, ks.vals_a);
+    WS_LAUNCH_CHECK(st, false);
+    uint64_t *kf;
+    uint32_t *vf;
+    rc = launch_sort_pairs((size_t)P, ks.keys_a, ks.keys_b, ks.vals_a, ks.vals_b, 32, ks.sort, st, false, &kf, &vf);
+    if (rc != WS_OK) return rc;
+    knn_box_minmax<<<(P + 1023) / 1024, 1024, 0, st>>>(P, points, vf, ks.boxes);
     WS_LAUNCH_CHECK(st, false);
     knn_box_mean_dist<<<(P + 255) / 256, 256, 0, st>>>(P, points, vf, ks.boxes, mean_dists);
     WS_LAUNCH_CHECK(st, false);

@@ -16,7 +16,7 @@ WS_ABI_VERSION = 3
 SYMBOLS = [
     "ws_abi_version", "ws_last_error", "ws_geom_bytes", "ws_image_bytes", "ws_binning_bytes",
     "ws_forward_prepare", "ws_forward_render", "ws_backward", "ws_mark_visible", "ws_knn_bytes",
-    "ws_knn_dist2", "ws_multi_instance_opt", "ws_sort_bytes", "ws_sort_pairs_u64", "ws_sort_pairs_u32", "ws_set_binning_mode",
+    "ws_knn_dist2", "ws_knn_dist2_static", "ws_multi_instance_opt", "ws_sort_bytes", "ws_sort_pairs_u64", "ws_sort_pairs_u32", "ws_set_binning_mode",
     "ws_loss_bytes", "ws_l1_ssim_forward", "ws_l1_ssim_backward", "ws_debug_fetch",
     "ws_adam_step", "ws_densify_stats", "ws_allreduce_sum_f32", "ws_allreduce_tune", "ws_allreduce_split",
     "ws_sharded_adam_step", "ws_densify_plan_bytes", "ws_densify_plan", "ws_densify_gather", "ws_reset_opacity",
@@ -25,6 +25,7 @@ SYMBOLS = [
     "ws_debug_fma_peak",
 ]
 WS_PROF_NSTAGES = 8
+WS_KNN_STATIC_MAX_POINTS = 300000  # include/wheatsplat.h
 
 
 class WsView(C.Structure):
@@ -119,6 +120,8 @@ def load():
     lib.ws_knn_bytes.argtypes = [i32]
     lib.ws_knn_dist2.restype = C.c_int
     lib.ws_knn_dist2.argtypes = [i32, vp, vp, vp, sz, vp]
+    lib.ws_knn_dist2_static.restype = C.c_int
+    lib.ws_knn_dist2_static.argtypes = [i32, vp, vp, vp]
     lib.ws_multi_instance_opt.restype = C.c_int
     lib.ws_multi_instance_opt.argtypes = [i32, i32, vp, f32, vp, vp]
     lib.ws_sort_bytes.restype = sz
