@@ -132,3 +132,35 @@ def test_vote_accumulator_sums_views_on_the_device():
     acc.join()   # the views ran on the accumulator's own streams
     assert torch.allclose(acc.all_counts, total, rtol=1e-5, atol=1e-6)
     assert torch.equal(acc.labels(), segment.multi_instance_opt(acc.all_counts))
+
+
+def test_vote_accumulator_keeps_dropped_inputs_alive_across_its_streams():
+    """The usual loop `mask = load(v).cuda(); acc.add_view(mask, ...)` drops the previous mask while the view's kernels
+    (on the accumulator's own stream) may not have read it yet.  Here the freed block is handed out again at once and
+    filled with another label on the caller's stream; the votes must still be those of the original masks."""
+    sc, cam_np, mask_np, ul, num_obj = cases.fsr_inputs("fsr_multi")
+    cams = scene.overhead_cameras(cam_np["image_width"], cam_np["image_height"])
+    g = {k: t(sc[k]) for k in ("means3D", "opacities", "shs", "scales", "rotations")}
+    P = sc["means3D"].shape[0]
+    views = (17, 5, 9, 22, 30, 2)
+    masks = [scene.head_masks(sc, cams[ci], n_labels=num_obj) for ci in views]
+
+    def run(streams, clobber):
+        acc = segment.VoteAccumulator(num_obj, P, streams=streams)
+        for ci, m in zip(views, masks):
+            mask = t(m)
+            rs = _settings(cams[ci], np.zeros(3, np.float32))
+            acc.add_view(mask, rs, g["means3D"], g["opacities"], shs=g["shs"], scales=g["scales"],
+                         rotations=g["rotations"])
+            if clobber:
+                shape = mask.shape
+                del mask
+                junk = torch.full(shape, float(num_obj), dtype=torch.float32, device="cuda")  # same size: same block if free
+                del junk
+        acc.join()
+        torch.cuda.synchronize()
+        return acc.all_counts.clone()
+
+    want = run(1, False)
+    got = run(3, True)
+    assert torch.allclose(got, want, rtol=1e-5, atol=1e-6)

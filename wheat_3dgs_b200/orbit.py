@@ -91,6 +91,10 @@ class StreamRing:
         st.wait_stream(torch.cuda.current_stream())
         return torch.cuda.stream(st)
 
+    def stream_of(self, i):
+        """Frame i's stream object, or None when the ring is the current stream only."""
+        return self.streams[i % self.n] if self.streams else None
+
     def fork(self):
         cur = torch.cuda.current_stream()
         for st in self.streams:

@@ -33,7 +33,11 @@ class VoteAccumulator:
         """`streams` > 1: consecutive add_view calls go on that many CUDA streams in turn (orbit.StreamRing): views are
         independent and the votes are float atomics into one accumulator, so one view's short binning kernels run
         under another's blend kernel (config 3: 729 -> 800 views/s).  `labels()` joins the streams first; the tuple
-        add_view returns belongs to the view's stream."""
+        add_view returns belongs to the view's stream (order your reads after it: `join()` or a stream wait).
+        Lifetimes are handled here: every CUDA tensor the caller passes is recorded on the view's stream
+        (Tensor.record_stream), so the usual loop `mask = load(v).cuda(); acc.add_view(mask, ...)` may drop or
+        overwrite-by-reallocation the previous mask at once -- the caching allocator does not hand the block out
+        again until the view's kernels have read it -- and the returned tensors are recorded on the caller's stream."""
         from .orbit import StreamRing
         self.num_obj = int(num_obj)
         self.all_counts = torch.zeros((self.num_obj + 1, int(P)), dtype=torch.float32, device=device)
@@ -45,13 +49,25 @@ class VoteAccumulator:
         rs = raster_settings
         e = torch.Tensor([])
         o = lambda t: e if t is None else t
+        view_stream, caller_stream = self._ring.stream_of(self._n), torch.cuda.current_stream()
         with self._ring.stream(self._n):
             self._n += 1
-            return _ops.flash_rasterize_gaussians(
+            out = _ops.flash_rasterize_gaussians(
                 gt_mask, unique_label, rs.bg, means3D, o(colors_precomp), opacities, o(scales), o(rotations),
                 rs.scale_modifier, o(cov3D_precomp), rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy,
                 rs.image_height, rs.image_width, o(shs), rs.sh_degree, rs.campos, rs.prefiltered, self.num_obj, rs.debug,
                 used_count_out=self.all_counts)
+        if view_stream is not None:
+            # the inputs were allocated on the caller's stream and are read asynchronously on the view's stream
+            for x in (gt_mask, unique_label, rs.bg, means3D, colors_precomp, opacities, scales, rotations, cov3D_precomp,
+                      rs.viewmatrix, rs.projmatrix, rs.campos, shs):
+                if torch.is_tensor(x) and x.is_cuda:
+                    x.record_stream(view_stream)
+            # the outputs were allocated on the view's stream and are used on the caller's
+            for x in out:
+                if torch.is_tensor(x) and x.is_cuda and x is not self.all_counts:
+                    x.record_stream(caller_stream)
+        return out
 
     def join(self):
         """The current stream waits for every view added so far (call before reading all_counts)."""
