@@ -113,6 +113,42 @@ def test_dropin_module_autograd_matches_golden(golden_dir):
     assert_exact("markVisible", G.n(vis), oracle.mark_visible(g["means3D"], cam["viewmatrix"]))
 
 
+def test_rasterizer_outputs_can_be_edited_in_place_like_the_references():
+    """The reference returns independently allocated tensors, so callers write `image.clamp_(0, 1)` or `depth[m] = 0`
+    on them before the loss.  Ours share one allocation; they must still not be autograd views of one base."""
+    import wheat_3dgs_b200
+    wheat_3dgs_b200.install()
+    from diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianRasterizer
+    g, cam, lg, deg = cases.dgr_inputs("dgr_sh3")
+    rs = GaussianRasterizationSettings(
+        image_height=cam["image_height"], image_width=cam["image_width"], tanfovx=cam["tanfovx"], tanfovy=cam["tanfovy"],
+        bg=G.t(cases.BG), scale_modifier=1.0, viewmatrix=G.t(cam["viewmatrix"]), projmatrix=G.t(cam["projmatrix"]),
+        sh_degree=deg, campos=G.t(cam["campos"]), prefiltered=False, debug=False)
+    grads = []
+    for inplace in (True, False):
+        leaf = {k: G.t(g[k]).requires_grad_(True) for k in ("means3D", "shs", "opacities", "scales", "rotations")}
+        means2D = torch.zeros_like(leaf["means3D"], requires_grad=True)
+        color, radii, depth, alpha = GaussianRasterizer(rs)(means3D=leaf["means3D"], means2D=means2D,
+                                                            opacities=leaf["opacities"], shs=leaf["shs"],
+                                                            scales=leaf["scales"], rotations=leaf["rotations"])
+        for x in (color, depth, alpha):
+            assert not x._is_view() and x.is_contiguous() and x.data_ptr() % 16 == 0
+        far = depth.detach() > float(depth.detach().mean())
+        if inplace:
+            color.clamp_(0.1, 0.6)
+            depth[far] = 0
+        else:
+            color, depth = color.clamp(0.1, 0.6), depth.masked_fill(far, 0.0)
+        # alpha is saved for the backward by the reference too (DGR __init__.py save_for_backward): editing it in place
+        # is an autograd error there as here, so it is only used out of place
+        alpha = alpha * 0.5
+        ((color * G.t(lg["dL_dcolor"])).sum() + (depth * G.t(lg["dL_ddepth"])).sum() + (alpha * G.t(lg["dL_dalpha"])).sum()).backward()
+        grads.append({k: v.grad.double() for k, v in leaf.items()})
+    for k in grads[0]:
+        a, b = grads[0][k], grads[1][k]
+        assert float((a - b).norm() / b.norm()) < 1e-4, k   # float atomics in a different order, nothing more
+
+
 @pytest.mark.parametrize("name", sorted(cases.FSR_CASES))
 def test_flashsplat_matches_reference_golden(golden_dir, name):
     gold = _gold(golden_dir, name)

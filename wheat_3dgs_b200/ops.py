@@ -151,14 +151,28 @@ def _binning_alloc(nbytes, dev):
     return base.narrow(0, 0, nbytes)
 
 
+def _output_planes(H, W, dev):
+    """color [3,H,W], depth [1,H,W], alpha [1,H,W] in ONE allocation, as three tensors of their own on the shared
+    storage (Tensor.set_), not views of a common base: autograd marks several views of one tensor returned from a
+    Function as outputs of a multi-output node and then refuses in-place edits of them (`image.clamp_()`,
+    `depth[m] = 0`), which the reference's independently allocated outputs allow.  Each part starts on a 256-byte
+    boundary whatever H*W is."""
+    hw = H * W
+    pad = lambda n: (n + 63) // 64 * 64   # floats
+    o_depth = pad(3 * hw)
+    o_alpha = o_depth + pad(hw)
+    storage = torch.empty((o_alpha + hw,), dtype=torch.float32, device=dev).untyped_storage()
+    part = lambda off, c: torch.empty((0,), dtype=torch.float32, device=dev).set_(storage, off, (c, H, W), (hw, W, 1))
+    return part(0, 3), part(o_depth, 1), part(o_alpha, 1)
+
+
 def _forward(call, flash):
     """Shared forward: returns (R, color, depth, alpha, radii, geom, binning, image)."""
     L = _lib.load()
     dev, P, H, W = call.device, call.P, call.H, call.W
-    # three allocations per call: the five output planes (color 3, depth, alpha: views of one tensor), radii, and one
+    # three allocations per call: the five output planes (color 3, depth, alpha share one allocation), radii, and one
     # byte buffer carved into the geometry and image scratch (512-byte aligned parts)
-    planes = torch.empty((5, H, W), dtype=torch.float32, device=dev)
-    color, depth, alpha = planes[0:3], planes[3:4], planes[4:5]
+    color, depth, alpha = _output_planes(H, W, dev)
     radii = torch.empty((P,), dtype=torch.int32, device=dev)
     gb, ib = (L.ws_geom_bytes(P) + 511) // 512 * 512, L.ws_image_bytes(W, H)
     scratch = torch.empty((gb + ib,), dtype=torch.uint8, device=dev)
