@@ -4,6 +4,7 @@
 #include <stdlib.h>
 #include <string.h>
 #include <mutex>
+#include <thread>
 #include <vector>
 #include "ws_common.cuh"
 
@@ -221,6 +222,21 @@ extern "C" size_t ws_binning_bytes(int64_t num_rendered, int32_t width, int32_t 
     return b + 256;
 }
 
+// One turn of the mailbox spin below: a pause hint for the sibling hyper-thread while the wait is short (the count
+// normally arrives within ~100 us), the scheduler's yield once it is not (a long view, a debugger, a contended host),
+// so a late kernel does not pin a host core.  Builds on x86-64 and aarch64 (Grace) hosts.
+static inline void cpu_relax(uint32_t spins)
+{
+    if (spins > (1u << 16)) { std::this_thread::yield(); return; }
+#if defined(__x86_64__) || defined(__i386__)
+    __builtin_ia32_pause();
+#elif defined(__aarch64__)
+    asm volatile("yield" ::: "memory");
+#else
+    std::this_thread::yield();
+#endif
+}
+
 extern "C" int64_t ws_forward_prepare(const ws_view *view, const ws_gaussians *g, int32_t *radii, void *geom,
                                       size_t geom_bytes, const ws_flash *fl, ws_stream_t stream)
 {
@@ -264,7 +280,7 @@ extern "C" int64_t ws_forward_prepare(const ws_view *view, const ws_gaussians *g
     for (uint32_t spins = 1;; spins++) {
         word = *mb;
         if ((uint32_t)(word >> 32) == seq) break;
-        __builtin_ia32_pause();
+        cpu_relax(spins);
         if ((spins & 1023u) == 0) {   // the kernel is gone (finished without our sequence number, or failed)?
             cudaError_t q = cudaEventQuery(ev);
             if (q == cudaSuccess) {
