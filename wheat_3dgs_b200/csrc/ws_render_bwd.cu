@@ -45,8 +45,12 @@ namespace ws {
 #ifndef WS_RB_NSTAGE
 #define WS_RB_NSTAGE 2
 #endif
+// CTAs per SM the register allocation is sized for.  Shared memory allows 11 (11 x (18688 + 1024) B = 211 KB of 228 KB;
+// 12 would need 236.5 KB), so 11 is what is asked for: ptxas then has 88 registers per thread to work with instead of
+// 80 (it uses 79; 76 at 12).  A/B on config 2, two rounds each (profiles/r03_ab_rb_minb.txt): 12: 0.9056 / 0.9072 ms,
+// 11: 0.9045 / 0.9057 ms, 10: 0.9294 / 0.9298 ms.
 #ifndef WS_RB_MINB
-#define WS_RB_MINB 12
+#define WS_RB_MINB 11
 #endif
 constexpr int RB_WARPS = WS_RB_WARPS;   // 8x8 pixel blocks (warps) per CTA: 2 = a 16x8 half tile, 4 = the tile
 constexpr int RB_THREADS = 32 * RB_WARPS;
