@@ -208,3 +208,29 @@ def test_raw_training_loop_at_odd_P_and_bucket_guard():
             img2.sum().backward()
     finally:
         rz.set_grad_bucket(None)
+
+
+def test_trainer_loop_head_sets_the_position_rate_and_raises_the_sh_degree():
+    """train_vanilla_3dgs.py:58-62 through Trainer.iteration(..., iteration=i): the xyz step of iteration i uses that
+    iteration's scheduled rate (a step with the rate at 30000 moves xyz ~100x less than one with the rate at 1), and
+    iteration 1000 renders with one more SH band."""
+    from wheat_3dgs_b200 import scene, train
+    P, W, H = 20000, 160, 120
+    sc = scene.synthetic_scene(P, seed=0, scale_median=0.004)
+    cam = scene.overhead_cameras(W, H)[17]
+    dev = torch.device("cuda")
+    t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+    cd = dict(cam, viewmatrix=t(cam["viewmatrix"]), projmatrix=t(cam["projmatrix"]), campos=t(cam["campos"]))
+    gt = torch.rand(3, H, W, device=dev)
+    bg = torch.zeros(3, device=dev)
+    moved = {}
+    for it in (1, 30000):
+        tr = train.Trainer(train.raw_params_from_scene(sc, dev), 2, dev)
+        before = tr.p["xyz"].detach().clone()
+        assert np.isfinite(float(tr.iteration(cd, gt, bg, iteration=it)))
+        assert tr.get_lr("xyz") == train.expon_lr(it, 0.00016, 0.0000016, max_steps=30000)
+        assert tr.active_sh_degree == (3 if it % 1000 == 0 else 2)
+        moved[it] = float((tr.p["xyz"].detach() - before).abs().max())
+    # first Adam step: |delta| = lr for every element with a non-zero gradient
+    # (float32 positions of magnitude ~1 resolve a 1.6e-6 step to within a few per cent)
+    assert abs(moved[1] / 0.0001599754409773643 - 1) < 1e-3 and abs(moved[30000] / 1.6e-06 - 1) < 0.08
