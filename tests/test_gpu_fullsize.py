@@ -18,7 +18,7 @@ import pytest
 import torch
 
 import cases
-from util import assert_bits, assert_exact, assert_image
+from util import GRAD_NAMES, assert_bits, assert_exact, assert_grad, assert_image
 from wheat_3dgs_b200 import scene
 
 pytestmark = pytest.mark.gpu
@@ -265,3 +265,93 @@ def test_fullsize_goldens(name):
         grads = {k: bench.sample(t) for k, t in zip(bench.GRAD_KEYS, out)}
     par = bench.compare_signature(gold, sig, samples, grads, name=name)
     assert par["ok"], par
+
+
+def _flash_backward(gd, cd, bg, deg, fw, mask, ul, dc, dd, da):
+    """ops.flash_rasterize_gaussians_backward (render_bwd<true>) on the buffers of a flashsplat forward."""
+    E = torch.Tensor([])
+    R, color, depth, alpha, radii, geom, binning, image = fw[:8]
+    return ops.flash_rasterize_gaussians_backward(
+        mask, ul if ul is not None else torch.tensor([], dtype=torch.int), bg, gd["means3D"], radii, E, gd["scales"],
+        gd["rotations"], 1.0, E, cd["viewmatrix"], cd["projmatrix"], cd["tanfovx"], cd["tanfovy"], dc, dd, da, gd["shs"],
+        deg, cd["campos"], geom, R, binning, image, alpha, False)
+
+
+@pytest.mark.parametrize("name", sorted(cases.FSR_CASES))
+def test_flash_backward_matches_oracle(name):
+    """The flashsplat backward (FSR backward.cu:455-462,529-536): with unique_label given, a Gaussian whose label is
+    >= 0 and differs from the pixel's mask id is skipped by that pixel -- no gradient from it, and it does not take
+    part in the pixel's transmittance walk.  Toy size against the CPU oracle (oracle/splat_oracle.c, render backward
+    with gt_mask / unique_label), with and without labels."""
+    import oracle
+    sc, cam, mask, ul, num_obj = cases.fsr_inputs(name)
+    if ul is None:   # the multi-label case has no labels of its own: gate a third of the heads, free another third
+        hid = sc["head_id"]
+        ul = np.where(hid < 0, -1, np.where(hid % 3 == 0, (hid % num_obj) + 1, np.where(hid % 3 == 1, 0, -1))).astype(np.int32)
+    H, W = cam["image_height"], cam["image_width"]
+    gd, cd = G.dev_inputs(sc, cam)
+    bg = torch.zeros(3, device="cuda")
+    lg = scene.loss_gradients((3, H, W), seed=4)
+    dc, dd, da = G.t(lg["dL_dcolor"]), G.t(lg["dL_ddepth"]), G.t(lg["dL_dalpha"])
+    gated_differs = False
+    for labels in (ul, None):
+        fw = G.flash_forward(gd, cd, bg, 3, G.t(mask), None if labels is None else G.t(labels), num_obj)
+        mine = _flash_backward(gd, cd, bg, 3, fw, G.t(mask), None if labels is None else G.t(labels), dc, dd, da)
+        of = oracle.forward(sc, cam, np.zeros(3, np.float32), sh_degree=3, gt_mask=mask, unique_label=labels,
+                            num_obj=num_obj)
+        ob = oracle.backward(sc, cam, np.zeros(3, np.float32), of, lg["dL_dcolor"], lg["dL_ddepth"], lg["dL_dalpha"],
+                             sh_degree=3, gt_mask=mask, unique_label=labels)
+        for k, m in zip(GRAD_NAMES, mine):
+            assert_grad("%s (%s)" % (k, "labels" if labels is not None else "no labels"), G.n(m).reshape(ob[k].shape), ob[k])
+        if labels is not None:
+            plain = oracle.backward(sc, cam, np.zeros(3, np.float32), of, lg["dL_dcolor"], lg["dL_ddepth"],
+                                    lg["dL_dalpha"], sh_degree=3)
+            gated_differs = float(np.abs(plain["dL_dopacity"] - ob["dL_dopacity"]).max()) > 1e-3 * float(np.abs(plain["dL_dopacity"]).max())
+    assert gated_differs, "the case does not exercise the label gate"
+
+
+@pytest.mark.skipif(not HAVE_FSR, reason="oracle/_ref/libref_fsr.so not built")
+def test_flash_backward_against_live_reference_cfg3_size():
+    """render_bwd<true> at P = 1 M, 2048x1536, 500 labels with the unique_label gate, against the unmodified flashsplat
+    rasterizer's backward run live.
+
+    Bar: every gradient tensor within 1e-3 norm-wise of the reference's (the gradient tier's relative tolerance).  The
+    element-wise form of the tier used for the DGR backward is NOT applied here, for a measured reason: on identical
+    inputs WITHOUT labels the two unmodified references themselves -- libref_fsr.so and libref_dgr.so, whose
+    backward.cu differ only by the gate -- disagree by 2.6e-4 to 2.8e-4 norm-wise in every gradient tensor
+    (deterministically: three FSR runs agree to 1e-6), while this library agrees with the DGR one to 7e-7 and its
+    FLASH and plain kernels with each other to 2e-7 (round 3, gpurun diagnostic).  The cause inside the flashsplat build
+    was not found; until it is, the reference's own two rasterizers bound how closely the FSR backward can be matched.
+    The gate itself is pinned exactly at toy size by test_flash_backward_matches_oracle above."""
+    P, W, H, nobj = 1000000, 2048, 1536, 500
+    sc = scene.synthetic_scene(P, seed=0)
+    cam = scene.overhead_cameras(W, H)[17]
+    gd, cd = G.dev_inputs(sc, cam)
+    bg = G.t(np.zeros(3, np.float32))
+    mask = G.t(scene.head_masks(sc, cam, n_labels=nobj))
+    hid = sc["head_id"]
+    ul = G.t(np.where(hid < 0, -1, np.where(hid % 3 == 0, hid + 1, np.where(hid % 3 == 1, 0, -1))).astype(np.int32))
+    lg = scene.loss_gradients((3, H, W), seed=2)
+    dc, dd, da = G.t(lg["dL_dcolor"]), G.t(lg["dL_ddepth"]), G.t(lg["dL_dalpha"])
+    nrm = lambda a, b: float((a.reshape(-1).double() - b.reshape(-1).double()).norm() / b.reshape(-1).double().norm())
+    for labels in (ul, None):
+        rr = refmod.RefRasterizer("fsr")
+        rr.forward(gd, cd, bg, 3, gt_mask=mask, unique_label=labels, num_obj=nobj, outputs={})
+        torch.cuda.synchronize()
+        ref = {k: v.clone() for k, v in rr.backward(dc, dd, da).items()}
+        torch.cuda.synchronize()
+        fw = G.flash_forward(gd, cd, bg, 3, mask, labels, nobj)
+        mine = _flash_backward(gd, cd, bg, 3, fw, mask, labels, dc, dd, da)
+        for k, m in zip(GRAD_NAMES, mine):
+            assert torch.isfinite(m).all(), k
+            assert nrm(m, ref[k]) < 1e-3, "%s (%s): norm-wise %g" % (k, "labels" if labels is not None else "no labels", nrm(m, ref[k]))
+        plain = G.backward(gd, cd, bg, 3, fw[:8], dc, dd, da)
+        if labels is None:
+            # without labels the FLASH kernel is the plain kernel
+            for k, m, q in zip(GRAD_NAMES, mine, plain):
+                assert nrm(m, q) < 1e-4, k
+        else:
+            # the gate is live in this case: the ungated walk over the gated forward's buffers (whose alpha no longer
+            # matches it) is far outside the bar, or not even finite
+            assert not (nrm(plain[2], ref["dL_dopacity"]) < 1e-2)
+        del rr, ref, fw, mine, plain
