@@ -204,16 +204,37 @@ class InputPrefetcher:
                        "ready": torch.cuda.Event(), "free": torch.cuda.Event()} for _ in range(2)]
         for sl in self.slots:
             sl["free"].record()
+        self.copies = []   # (start event, end event, bytes) of every step's upload, on the copy stream
 
     def prefetch(self, i):
         v = self.view_of(i)
         sl = self.slots[i & 1]
         with self.torch.cuda.stream(self.stream):
             self.stream.wait_event(sl["free"])  # the step that last read this slot has finished with it
+            t0 = self.torch.cuda.Event(enable_timing=True)
+            t0.record(self.stream)
             sl["cam"].copy_(self.cam_host[v], non_blocking=True)
+            nbytes = sl["cam"].numel() * 4
             if sl["gt"] is not None:
                 sl["gt"].copy_(self.imgs[v % len(self.imgs)], non_blocking=True)
+                nbytes += sl["gt"].numel() * 4
             sl["ready"].record(self.stream)
+            t1 = self.torch.cuda.Event(enable_timing=True)
+            t1.record(self.stream)
+            self.copies.append((t0, t1, nbytes))
+
+    def copy_stats(self, last_n):
+        """Duration of the last `last_n` uploads as the copy stream saw them (CUDA events either side of the copies,
+        while the previous step's kernels run beside them): mean / max milliseconds and the mean rate in GB/s.  Call
+        after the device has drained."""
+        c = self.copies[-last_n:] if last_n > 0 else []
+        if not c:
+            return None
+        ms = [a.elapsed_time(b) for a, b, _ in c]
+        nb = sum(n for _, _, n in c) / len(c)
+        mean = sum(ms) / len(ms)
+        return {"h2d_ms_mean": mean, "h2d_ms_max": max(ms), "h2d_gbs": nb / (mean * 1e-3) / 1e9 if mean > 0 else None,
+                "copies": len(c)}
 
     def take(self, i, last):
         """Inputs of step i (waits for their copy); starts the copy of step i+1's unless `last`."""
@@ -577,6 +598,8 @@ def run_fwdbwd(args, job):
     e1.record()
     job.barrier()
     ms_e2e = wdist.max_over_ranks(e0.elapsed_time(e1), dev)
+    torch.cuda.synchronize()
+    h2d_stats = pre.copy_stats(args.steps)   # this rank's uploads of the timed steps
     rz.set_grad_bucket(None)
     del params, means2D, pre, gts
 
@@ -619,7 +642,7 @@ def run_fwdbwd(args, job):
     fma = {"ffma2_tflops": ops.fma_peak(True, dev), "ffma_tflops": ops.fma_peak(False, dev)} if rank == 0 else None
     return dict(P=P, W=W, H=H, nv=nv, M=M, ms_total=ms_total, ms_e2e=ms_e2e, launches=launches, clocks=clocks,
                 reduce_how=reduce_how, prof=prof, nprof=nprof, stats=stats, h2d=h2d, d2h=4, parity=parity,
-                exchange_check=xchk, exchange_split=xsplit, fma=fma)
+                exchange_check=xchk, exchange_split=xsplit, fma=fma, h2d_stats=h2d_stats)
 
 
 # ----------------------------------------------------------------------------- full training iteration
@@ -1170,6 +1193,22 @@ METRICS = {
 }
 
 
+def e2e_split(e2e_ms, device_ms, h2d):
+    """What one end-to-end step is made of, so the line says what bounds it: the step as timed end to end, the same
+    step with inputs resident (the line's ms_per_step), and the upload of one step's inputs as its own stream saw it
+    (rank 0's; it runs beside the previous step's kernels).  The upload is prefetched one step ahead, so a step cannot
+    be shorter than the longer of the two; what is left above that is host time between launches (Python, autograd).
+    bound: "h2d" / "device" = the longer of the two legs, when the step is within 10 % of it; else "host"."""
+    out = {"e2e_ms_per_step": e2e_ms, "device_ms_per_step": device_ms}
+    if not h2d:
+        return out
+    out.update(h2d_ms_per_step=h2d["h2d_ms_mean"], h2d_ms_max=h2d["h2d_ms_max"], h2d_gbs=h2d["h2d_gbs"])
+    floor = max(h2d["h2d_ms_mean"], device_ms)
+    out["bound"] = "host" if e2e_ms > 1.10 * floor else ("h2d" if h2d["h2d_ms_mean"] >= device_ms else "device")
+    out["over_floor_ms"] = e2e_ms - floor
+    return out
+
+
 def describe(workload):
     wl = WORKLOADS[workload]
     shape = "%dK Gaussians SH3, %dx%d" % (wl["P"] // 1000, wl["W"], wl["H"]) if wl["P"] < 1000000 else \
@@ -1335,6 +1374,7 @@ def main():
                     parity=r["parity"],
                     e2e={"value": world * args.steps / (r["ms_e2e"] * 1e-3), "unit": "views/s",
                          "h2d_bytes_per_step": r["h2d"], "d2h_bytes_per_step": r["d2h"]})
+        line["e2e"].update(e2e_split(r["ms_e2e"] / args.steps, r["ms_total"] / args.steps, r.get("h2d_stats")))
         if extra:
             line["extra"] = extra
         if world > 1:
