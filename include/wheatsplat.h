@@ -306,7 +306,9 @@ int ws_allreduce_sum_f32(int32_t rank, int32_t world, int64_t numel, void *multi
 /* Tuning knobs of the multimem kernel (process-wide): independent 16-byte ld_reduce in flight per thread (2, 4 or 8;
  * default 4) and threads per CTA (default 512). */
 int ws_allreduce_tune(int32_t unroll, int32_t threads);
-/* With both a multicast address and peer pointers: the first `multicast_permille` thousandths of every rank's slice are
+/* EXPERIMENTAL, off by default and not part of the stable ABI (measured slower than the switch-only kernel at every
+ * setting on 8 B200s, profiles/r02_exchange_split_sweep_8gpu.jsonl; kept for re-measurement on other fabrics).
+ * With both a multicast address and peer pointers: the first `multicast_permille` thousandths of every rank's slice are
  * reduced through the switch (multimem), the rest at the same time by `peer_ctas` extra CTAs with peer loads and
  * stores (the in-switch reduction runs at about half the link rate; the peer path fills the links).  1000 = switch
  * only (default).  Process-wide. */
